@@ -1,0 +1,451 @@
+// ffmpc_engine.cu -- host side of the C ABI in include/ffmpc.h: handle, workspace in HBM, the
+// fixed launch sequence of one batched FDDP / Box-FDDP solve, host<->device staging.
+//
+// The product build is nvcc -gencode arch=compute_100a,code=sm_100a only (see __graft_entry__.build);
+// there is NO CPU execution path: without a CUDA device ffmpc_create fails with FFMPC_ERR_NO_DEVICE.
+// (tests/host_emul compiles this same file against a fiber-based CUDA emulator, FFMPC_EMU, purely to
+// run the kernel sources in CPU CI; that build is a separate test-only library.)
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "ffmpc_launch.h"
+
+using namespace ffmpc;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) return fail(FFMPC_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+};
+
+}  // namespace
+
+struct ffmpc_handle {
+  int device = 0;
+  int max_batch = 0;
+  int N = 0, nx = 0;
+  ffmpc_config cfg;
+  ffmpc_model mdl;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::vector<void *> allocs;
+  Workspace ws;  // device pointers of the internal workspace
+  // device staging for the host API
+  int *d_mode = nullptr;
+  double *d_x0 = nullptr, *d_pref = nullptr, *d_vref = nullptr, *d_xreg = nullptr, *d_tauref = nullptr, *d_xsinit = nullptr,
+         *d_usinit = nullptr;
+  double *o_xs = nullptr, *o_us = nullptr, *o_K = nullptr, *o_k = nullptr, *o_cost = nullptr, *o_stop = nullptr, *o_gaps = nullptr,
+         *o_fpred = nullptr;
+  int *o_iters = nullptr, *o_ok = nullptr;
+  double last_ms = 0.0;
+  int last_launches = 0;
+  bool timing_valid = false;
+};
+
+namespace {
+
+template <class T> int dalloc(ffmpc_handle *h, T **p, size_t count) {
+  void *q = nullptr;
+  CU(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+  h->allocs.push_back(q);
+  *p = (T *)q;
+  return FFMPC_OK;
+}
+
+int check_cfg(const ffmpc_config *c) {
+  if (!c) return fail(FFMPC_ERR_ARG, "null config");
+  if (c->variant != FFMPC_VARIANT_CLASSICAL && c->variant != FFMPC_VARIANT_FF) return fail(FFMPC_ERR_ARG, "config.variant must be 0 (classical) or 1 (force-feedback)");
+  if (c->horizon < 1 || c->horizon > 4096) return fail(FFMPC_ERR_ARG, "config.horizon out of range");
+  if (c->contact_nc != 1 && c->contact_nc != 3) return fail(FFMPC_ERR_ARG, "config.contact_nc must be 1 (normal_1d) or 3 (point3d)");
+  if (!(c->dt_ocp > 0.0)) return fail(FFMPC_ERR_ARG, "config.dt_ocp must be > 0");
+  if (c->n_alphas < 1 || c->n_alphas > 32) return fail(FFMPC_ERR_ARG, "config.n_alphas out of range");
+  if (c->boxqp_maxiter < 1) return fail(FFMPC_ERR_ARG, "config.boxqp_maxiter must be >= 1");
+  return FFMPC_OK;
+}
+
+int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
+  Params P;
+  P.mdl = h->mdl;
+  P.cfg = h->cfg;
+  P.ws = h->ws;
+  const Workspace &ws = P.ws;
+  const int B = ws.B, N = ws.N;
+  cudaStream_t st = h->stream;
+  launches = 0;
+  FFMPC_LAUNCH(k_build_perm, 1, 1024, 1025 * sizeof(int), st, ws);
+  FFMPC_LAUNCH(k_init_state, (B + 127) / 128, 128, 0, st, P);
+  {
+    const size_t total = (size_t)B * (N + 1) * ws.nx;
+    const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+    FFMPC_LAUNCH(k_init_traj, grid, 256, 0, st, ws);
+  }
+  launches += 3;
+  for (int it = 0; it < max_iters; ++it) {
+    launch_node_diff(P, st);
+    launch_backward(P, st);
+    launch_forward(P, it, st);
+    launches += 5;
+  }
+  CU(cudaGetLastError());
+  return FFMPC_OK;
+}
+
+int launch_export(ffmpc_handle *h, const ffmpc_batch_out *out, int &launches) {
+  ExportPtrs o;
+  o.xs = out->xs; o.us = out->us; o.K = out->K; o.k = out->k; o.cost = out->cost; o.stop = out->stop;
+  o.gaps = out->gaps; o.f_pred = out->f_pred; o.iters = out->iters; o.ok = out->ok;
+  const size_t total = (size_t)h->ws.B * h->ws.N * NJ * h->ws.nx;
+  const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+  FFMPC_LAUNCH(k_export, grid, 256, 0, h->stream, h->ws, o);
+  launches += 1;
+  CU(cudaGetLastError());
+  return FFMPC_OK;
+}
+
+int bind_inputs(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters) {
+  if (!in) return fail(FFMPC_ERR_ARG, "null batch_in");
+  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
+  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
+  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
+  if (max_iters < 0) return fail(FFMPC_ERR_ARG, "max_iters must be >= 0");
+  Workspace &ws = h->ws;
+  ws.B = in->B;
+  ws.max_iters = max_iters;
+  ws.fixed_iters = fixed_iters;
+  ws.mode = in->mode;
+  ws.x0 = in->x0;
+  ws.p_ref = in->p_ref;
+  ws.v_ref = in->v_ref;
+  ws.x_reg_ref = in->x_reg_ref;
+  ws.tau_ref_in = in->tau_ref;
+  ws.xs_init = in->xs_init;
+  ws.us_init = in->us_init;
+  return FFMPC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void ffmpc_default_config(ffmpc_config *c, int variant) {
+  std::memset(c, 0, sizeof(*c));
+  const bool ff = variant == FFMPC_VARIANT_FF;
+  c->variant = variant;
+  c->horizon = 20;
+  c->contact_nc = 1;
+  c->use_box_fddp = 1;
+  c->use_inner_state_reg = 1;
+  c->use_inner_tau_reg = 1;
+  c->dt_ocp = 0.01;
+  c->w_ee_pos = 2.0e2;
+  c->w_ee_ori = 1.0e1;
+  c->ori_weights[0] = 2.0; c->ori_weights[1] = 2.0; c->ori_weights[2] = 0.15;
+  c->R_des[0] = c->R_des[4] = c->R_des[8] = 1.0;
+  c->w_posture = 5.0e-1;
+  c->w_v = 2.5e-1;
+  const double vd[7] = {1.0, 1.0, 1.0, 1.0, 0.4, 0.4, 0.4}, tl[7] = {87, 87, 87, 87, 12, 12, 12};
+  for (int i = 0; i < 7; ++i) {
+    c->v_damp_weights[i] = vd[i];
+    c->tau_limits[i] = tl[i];
+    c->q_soft_lb[i] = -std::numeric_limits<double>::infinity();
+    c->q_soft_ub[i] = std::numeric_limits<double>::infinity();
+  }
+  c->w_q_soft_limits = ff ? 8.0 : 0.0;
+  c->w_wdamp = 2.0e1;
+  c->w_wdamp_weights[0] = 1.5; c->w_wdamp_weights[1] = 1.5; c->w_wdamp_weights[2] = 0.2;
+  c->w_tau = 1.0e-3;
+  c->w_tau_soft_limits = ff ? 1.5 : 0.0;
+  c->tau_soft_limit_margin = 0.2;
+  c->z_press = 0.0020;
+  c->w_tangent_pos = 2.0e2; c->w_tangent_vel = 1.0e2;
+  c->w_unilateral = 5.0e1; c->friction_margin = 1e-3; c->w_fn = 2.0e1; c->fn_des = 8.0;
+  c->contact_gains[0] = 0.0; c->contact_gains[1] = 60.0; c->contact_inv_damping = 1.0e-8;
+  c->ff_alpha = exp(-2.0 * 3.14159265358979323846 * 18.0 * 0.01);
+  c->w_w = 8.0e-4; c->w_w_soft_limits = 2.0; c->w_y = 3.0e-3;
+  const double yq[7] = {0.2, 0.2, 0.2, 0.2, 0.1, 0.1, 0.1}, yv[7] = {0.08, 0.08, 0.08, 0.08, 0.05, 0.05, 0.05},
+               yt[7] = {0.35, 0.35, 0.35, 0.35, 0.2, 0.2, 0.2};
+  for (int i = 0; i < 7; ++i) { c->y_reg_weights[i] = yq[i]; c->y_reg_weights[7 + i] = yv[i]; c->y_reg_weights[14 + i] = yt[i]; }
+  c->reg_min = 1e-9; c->reg_max = 1e9; c->reg_incfactor = 10.0; c->reg_decfactor = 10.0;
+  c->th_stepdec = 0.5; c->th_stepinc = 0.01; c->th_acceptstep = 0.1; c->th_acceptnegstep = 2.0; c->th_grad = 1e-12;
+  c->th_stop = 5e-5;
+  c->n_alphas = 10;
+  c->boxqp_maxiter = 100; c->boxqp_th_acceptstep = 0.1; c->boxqp_th_grad = 1e-5; c->boxqp_reg = 0.0;
+}
+
+int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch, ffmpc_handle **out) {
+  if (!out) return fail(FFMPC_ERR_ARG, "null out handle");
+  *out = nullptr;
+  if (int e = check_cfg(cfg)) return e;
+  if (!model) return fail(FFMPC_ERR_ARG, "null model");
+  if (max_batch < 1) return fail(FFMPC_ERR_ARG, "max_batch must be >= 1");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+    return fail(FFMPC_ERR_NO_DEVICE, "no CUDA device visible: the ffmpc engine has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(FFMPC_ERR_ARG, "device index out of range");
+  CU(cudaSetDevice(device));
+  ffmpc_handle *h = new ffmpc_handle();
+  h->device = device;
+  h->max_batch = max_batch;
+  h->cfg = *cfg;
+  h->mdl = *model;
+  h->N = cfg->horizon;
+  h->nx = cfg->variant == FFMPC_VARIANT_FF ? 21 : 14;
+  const size_t B = (size_t)max_batch, N = (size_t)h->N, nx = (size_t)h->nx;
+  Workspace &ws = h->ws;
+  std::memset(&ws, 0, sizeof(ws));
+  ws.N = h->N;
+  ws.nx = h->nx;
+  int rc = FFMPC_OK;
+#define DA(ptr, count) if (rc == FFMPC_OK) rc = dalloc(h, &(ptr), (count))
+  if (cudaStreamCreate(&h->stream) != cudaSuccess) rc = fail(FFMPC_ERR_CUDA, "cudaStreamCreate failed");
+  if (rc == FFMPC_OK && (cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess)) rc = fail(FFMPC_ERR_CUDA, "cudaEventCreate failed");
+  DA(ws.tau_ref, B * NJ);
+  DA(ws.perm, B);
+  DA(ws.counts, 2);
+  DA(ws.xs, 2 * B * (N + 1) * nx);
+  DA(ws.us, 2 * B * N * NJ);
+  DA(ws.fs, B * (N + 1) * nx);
+  DA(ws.rec, B * (N + 1) * REC_SIZE);
+  DA(ws.ncost, B * (N + 1));
+  DA(ws.K, B * N * NJ * nx);
+  DA(ws.k, B * N * NJ);
+  DA(ws.Vfs, B * (N + 1) * nx);
+  DA(ws.preg, B); DA(ws.cost, B); DA(ws.dg, B); DA(ws.dq, B); DA(ws.stop, B); DA(ws.d1, B); DA(ws.d2, B);
+  DA(ws.feas, B); DA(ws.wasfeas, B); DA(ws.recalc, B); DA(ws.done, B); DA(ws.ok, B); DA(ws.iter, B); DA(ws.cur, B);
+  DA(ws.cost_valid, B);
+  DA(ws.f_pred, B * 6);
+#undef DA
+  if (rc != FFMPC_OK) {
+    ffmpc_destroy(h);
+    return rc;
+  }
+  if (prepare_backward() != 0) {
+    ffmpc_destroy(h);
+    return fail(FFMPC_ERR_CUDA, "cudaFuncSetAttribute(k_backward, MaxDynamicSharedMemorySize) failed");
+  }
+  *out = h;
+  return FFMPC_OK;
+}
+
+void ffmpc_destroy(ffmpc_handle *h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  for (void *p : h->allocs) cudaFree(p);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters, const ffmpc_batch_out *out,
+                      void *stream) {
+  if (!h || !out) return fail(FFMPC_ERR_ARG, "null handle / out");
+  CU(cudaSetDevice(h->device));
+  if (int e = bind_inputs(h, in, max_iters, fixed_iters)) return e;
+  cudaStream_t saved = h->stream;
+  if (stream) h->stream = (cudaStream_t)stream;
+  int launches = 0, l2 = 0;
+  int rc = launch_solve(h, max_iters, launches);
+  if (rc == FFMPC_OK) rc = launch_export(h, out, l2);
+  h->stream = saved;
+  h->last_launches = launches + l2;
+  h->timing_valid = false;
+  return rc;
+}
+
+int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
+                           const ffmpc_batch_out *out) {
+  if (!h || !out || !in) return fail(FFMPC_ERR_ARG, "null handle / in / out");
+  CU(cudaSetDevice(h->device));
+  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
+  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
+  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
+  const size_t Bm = (size_t)h->max_batch, B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx;
+  int rc = FFMPC_OK;
+#define DA(ptr, count) if (rc == FFMPC_OK && !(ptr)) rc = dalloc(h, &(ptr), (count))
+  DA(h->d_mode, Bm); DA(h->d_x0, Bm * nx); DA(h->d_pref, Bm * (N + 1) * 3); DA(h->d_vref, Bm * (N + 1) * 3); DA(h->d_xreg, Bm * 14);
+  if (in->tau_ref) DA(h->d_tauref, Bm * NJ);
+  if (in->xs_init) DA(h->d_xsinit, Bm * (N + 1) * nx);
+  if (in->us_init) DA(h->d_usinit, Bm * N * NJ);
+  if (out->xs) DA(h->o_xs, Bm * (N + 1) * nx);
+  if (out->us) DA(h->o_us, Bm * N * NJ);
+  if (out->K) DA(h->o_K, Bm * N * NJ * nx);
+  if (out->k) DA(h->o_k, Bm * N * NJ);
+  if (out->cost) DA(h->o_cost, Bm);
+  if (out->stop) DA(h->o_stop, Bm);
+  if (out->gaps) DA(h->o_gaps, Bm * (N + 1) * nx);
+  if (out->f_pred) DA(h->o_fpred, Bm * 6);
+  if (out->iters) DA(h->o_iters, Bm);
+  if (out->ok) DA(h->o_ok, Bm);
+#undef DA
+  if (rc != FFMPC_OK) return rc;
+  cudaStream_t st = h->stream;
+#define H2D(dst, src, count, T) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyHostToDevice, st))
+  H2D(h->d_mode, in->mode, B, int);
+  H2D(h->d_x0, in->x0, B * nx, double);
+  H2D(h->d_pref, in->p_ref, B * (N + 1) * 3, double);
+  H2D(h->d_vref, in->v_ref, B * (N + 1) * 3, double);
+  H2D(h->d_xreg, in->x_reg_ref, B * 14, double);
+  if (in->tau_ref) H2D(h->d_tauref, in->tau_ref, B * NJ, double);
+  if (in->xs_init) H2D(h->d_xsinit, in->xs_init, B * (N + 1) * nx, double);
+  if (in->us_init) H2D(h->d_usinit, in->us_init, B * N * NJ, double);
+#undef H2D
+  ffmpc_batch_in din;
+  din.B = in->B;
+  din.mode = h->d_mode; din.x0 = h->d_x0; din.p_ref = h->d_pref; din.v_ref = h->d_vref; din.x_reg_ref = h->d_xreg;
+  din.tau_ref = in->tau_ref ? h->d_tauref : nullptr;
+  din.xs_init = in->xs_init ? h->d_xsinit : nullptr;
+  din.us_init = in->us_init ? h->d_usinit : nullptr;
+  ffmpc_batch_out dout;
+  dout.xs = out->xs ? h->o_xs : nullptr; dout.us = out->us ? h->o_us : nullptr; dout.K = out->K ? h->o_K : nullptr;
+  dout.k = out->k ? h->o_k : nullptr; dout.cost = out->cost ? h->o_cost : nullptr; dout.stop = out->stop ? h->o_stop : nullptr;
+  dout.gaps = out->gaps ? h->o_gaps : nullptr; dout.f_pred = out->f_pred ? h->o_fpred : nullptr;
+  dout.iters = out->iters ? h->o_iters : nullptr; dout.ok = out->ok ? h->o_ok : nullptr;
+  if (int e = bind_inputs(h, &din, max_iters, fixed_iters)) return e;
+  int launches = 0, l2 = 0;
+  CU(cudaEventRecord(h->ev0, st));
+  rc = launch_solve(h, max_iters, launches);
+  if (rc == FFMPC_OK) rc = launch_export(h, &dout, l2);
+  CU(cudaEventRecord(h->ev1, st));
+  if (rc != FFMPC_OK) return rc;
+#define D2H(dst, src, count, T) if (dst) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyDeviceToHost, st))
+  D2H(out->xs, h->o_xs, B * (N + 1) * nx, double);
+  D2H(out->us, h->o_us, B * N * NJ, double);
+  D2H(out->K, h->o_K, B * N * NJ * nx, double);
+  D2H(out->k, h->o_k, B * N * NJ, double);
+  D2H(out->cost, h->o_cost, B, double);
+  D2H(out->stop, h->o_stop, B, double);
+  D2H(out->gaps, h->o_gaps, B * (N + 1) * nx, double);
+  D2H(out->f_pred, h->o_fpred, B * 6, double);
+  D2H(out->iters, h->o_iters, B, int);
+  D2H(out->ok, h->o_ok, B, int);
+#undef D2H
+  CU(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  h->last_ms = ms;
+  h->last_launches = launches + l2;
+  h->timing_valid = true;
+  return FFMPC_OK;
+}
+
+int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const int *inst, const int *knot, const double *x,
+                         const double *u, const ffmpc_node_out *out) {
+  if (!h || !in || !out || !inst || !knot || !x || !u) return fail(FFMPC_ERR_ARG, "null argument");
+  if (M < 1) return fail(FFMPC_ERR_ARG, "M must be >= 1");
+  CU(cudaSetDevice(h->device));
+  if (in->B < 1 || in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch size out of range");
+  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
+  for (int m = 0; m < M; ++m)
+    if (inst[m] < 0 || inst[m] >= in->B || knot[m] < 0 || knot[m] > h->N) return fail(FFMPC_ERR_ARG, "inst / knot out of range");
+  const size_t B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx, Ms = (size_t)M;
+  cudaStream_t st = h->stream;
+  // transient device buffers (test hook, not a hot path)
+  std::vector<void *> tmp;
+  auto talloc = [&](size_t bytes) -> void * {
+    void *p = nullptr;
+    if (cudaMalloc(&p, std::max<size_t>(bytes, 8)) != cudaSuccess) return nullptr;
+    tmp.push_back(p);
+    return p;
+  };
+  auto cleanup = [&]() { for (void *p : tmp) cudaFree(p); };
+  auto up = [&](const void *src, size_t bytes) -> void * {
+    void *p = talloc(bytes);
+    if (p) cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, st);
+    return p;
+  };
+  ffmpc_batch_in din;
+  din.B = in->B;
+  din.mode = (const int *)up(in->mode, B * sizeof(int));
+  din.x0 = (const double *)up(in->x0, B * nx * 8);
+  din.p_ref = (const double *)up(in->p_ref, B * (N + 1) * 24);
+  din.v_ref = (const double *)up(in->v_ref, B * (N + 1) * 24);
+  din.x_reg_ref = (const double *)up(in->x_reg_ref, B * 14 * 8);
+  din.tau_ref = in->tau_ref ? (const double *)up(in->tau_ref, B * NJ * 8) : nullptr;
+  din.xs_init = nullptr;
+  din.us_init = nullptr;
+  NodeEvalArgs A;
+  A.M = M;
+  A.inst = (const int *)up(inst, Ms * sizeof(int));
+  A.knot = (const int *)up(knot, Ms * sizeof(int));
+  A.x = (const double *)up(x, Ms * nx * 8);
+  A.u = (const double *)up(u, Ms * NJ * 8);
+  A.xnext = (double *)talloc(Ms * nx * 8); A.cost = (double *)talloc(Ms * 8); A.force = (double *)talloc(Ms * 24);
+  A.Fx = (double *)talloc(Ms * nx * nx * 8); A.Fu = (double *)talloc(Ms * nx * NJ * 8); A.Lx = (double *)talloc(Ms * nx * 8);
+  A.Lu = (double *)talloc(Ms * NJ * 8); A.Lxx = (double *)talloc(Ms * nx * nx * 8); A.Lxu = (double *)talloc(Ms * nx * NJ * 8);
+  A.Luu = (double *)talloc(Ms * NJ * NJ * 8);
+  for (void *p : tmp)
+    if (!p) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
+  if (!din.mode || !A.Luu) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
+  if (int e = bind_inputs(h, &din, 0, 1)) { cleanup(); return e; }
+  Params P;
+  P.mdl = h->mdl;
+  P.cfg = h->cfg;
+  P.ws = h->ws;
+  FFMPC_LAUNCH(k_init_state, (in->B + 127) / 128, 128, 0, st, P);  // resolves tau_ref
+  launch_node_eval(P, A, st);
+  cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess) { cleanup(); return fail(FFMPC_ERR_CUDA, std::string("node_eval launch: ") + cudaGetErrorString(le)); }
+  auto down = [&](void *dst, const void *src, size_t bytes) { if (dst) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st); };
+  down(out->xnext, A.xnext, Ms * nx * 8); down(out->cost, A.cost, Ms * 8); down(out->force, A.force, Ms * 24);
+  down(out->Fx, A.Fx, Ms * nx * nx * 8); down(out->Fu, A.Fu, Ms * nx * NJ * 8); down(out->Lx, A.Lx, Ms * nx * 8);
+  down(out->Lu, A.Lu, Ms * NJ * 8); down(out->Lxx, A.Lxx, Ms * nx * nx * 8); down(out->Lxu, A.Lxu, Ms * nx * NJ * 8);
+  down(out->Luu, A.Luu, Ms * NJ * NJ * 8);
+  cudaError_t se = cudaStreamSynchronize(st);
+  cleanup();
+  if (se != cudaSuccess) return fail(FFMPC_ERR_CUDA, std::string("node_eval: ") + cudaGetErrorString(se));
+  return FFMPC_OK;
+}
+
+int ffmpc_last_timing(ffmpc_handle *h, double *kernel_ms, int *launches) {
+  if (!h) return fail(FFMPC_ERR_ARG, "null handle");
+  if (kernel_ms) *kernel_ms = h->timing_valid ? h->last_ms : -1.0;
+  if (launches) *launches = h->last_launches;
+  return FFMPC_OK;
+}
+
+int ffmpc_sync(ffmpc_handle *h) {
+  if (!h) return fail(FFMPC_ERR_ARG, "null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  return FFMPC_OK;
+}
+
+const char *ffmpc_last_error(void) { return g_err.c_str(); }
+
+const char *ffmpc_version(void) {
+#ifdef FFMPC_EMU
+  return "ffmpc-b200 0.1 (CPU EMULATION TEST BUILD - not the product)";
+#else
+  return "ffmpc-b200 0.1 (sm_100a)";
+#endif
+}
+
+// sizes of the ABI structs, for the ctypes mirror self-check
+void ffmpc_abi_sizes(int *sizes) {
+  sizes[0] = (int)sizeof(ffmpc_model);
+  sizes[1] = (int)sizeof(ffmpc_config);
+  sizes[2] = (int)sizeof(ffmpc_batch_in);
+  sizes[3] = (int)sizeof(ffmpc_batch_out);
+  sizes[4] = (int)sizeof(ffmpc_node_out);
+}
+
+}  // extern "C"

@@ -1,0 +1,31 @@
+// ffmpc_launch.h -- host-callable launchers; each family of kernels lives in its own translation
+// unit so that it can be compiled with its own ptxas options (see __graft_entry__.build()).
+#pragma once
+#ifdef FFMPC_EMU
+#include "cuda_emu.h"
+#else
+#include <cuda_runtime.h>
+#endif
+#include "ffmpc_kernels.cuh"
+
+#ifdef FFMPC_EMU
+#define FFMPC_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  emu::launch(dim3(grid), dim3(block), (smem), [&]() { kernel(__VA_ARGS__); })
+#else
+#define FFMPC_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
+
+namespace ffmpc {
+constexpr int kNodeBlock = 128;
+constexpr int kBwdWarps = 4;
+constexpr int kFwdBlock = 64;
+
+// ffmpc_launch_node.cu
+void launch_node_diff(const Params &P, cudaStream_t st);
+void launch_node_eval(const Params &P, const NodeEvalArgs &A, cudaStream_t st);
+// ffmpc_launch_bwd.cu
+int prepare_backward();
+void launch_backward(const Params &P, cudaStream_t st);
+// ffmpc_launch_fwd.cu
+void launch_forward(const Params &P, int it, cudaStream_t st);
+}  // namespace ffmpc

@@ -1,0 +1,144 @@
+"""ctypes loader and thin Python front-end of ``libffmpc_b200.so`` (the CUDA engine).
+
+There is no fallback: if the shared library is missing, or no CUDA device is visible, construction
+raises.  PyTorch is used only for device buffers / streams (``solve_device``); numpy for the host API.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+from . import _abi
+from .batch import (BatchInputs, OUTPUT_NAMES, alloc_node_outputs, alloc_outputs, node_outputs_abi, outputs_abi, ptr)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libffmpc_b200.so")
+_lib = None
+
+
+class FFMPCError(RuntimeError):
+    pass
+
+
+def _declare(lib):
+    lib.ffmpc_last_error.restype = C.c_char_p
+    lib.ffmpc_version.restype = C.c_char_p
+    lib.ffmpc_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    lib.ffmpc_destroy.argtypes = [C.c_void_p]
+    lib.ffmpc_destroy.restype = None
+    lib.ffmpc_solve_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    lib.ffmpc_solve_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.ffmpc_node_eval_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ffmpc_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    lib.ffmpc_sync.argtypes = [C.c_void_p]
+    return lib
+
+
+def load_library(path: Optional[str] = None):
+    """Load the CUDA engine. Raises ``FFMPCError`` if it has not been built (``__graft_entry__.build()``)."""
+    global _lib
+    if path is None:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise FFMPCError(
+                f"{LIB_PATH} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()'). "
+                "The engine has no CPU fallback."
+            )
+        _lib = _declare(C.CDLL(LIB_PATH))
+        return _lib
+    return _declare(C.CDLL(path))
+
+
+class FFMPCEngine:
+    """One handle per GPU (``ffmpc_create``)."""
+
+    def __init__(self, cfg: _abi.Config, model: _abi.Model, device: int = 0, max_batch: int = 1, _lib=None):
+        self.lib = _lib if _lib is not None else load_library()
+        self.cfg, self.model = cfg, model
+        self.N = int(cfg.horizon)
+        self.nx = 21 if cfg.variant == _abi.VARIANT_FF else 14
+        self.max_batch = int(max_batch)
+        self.device = int(device)
+        self._h = C.c_void_p()
+        rc = self.lib.ffmpc_create(C.byref(cfg), C.byref(model), self.device, self.max_batch, C.byref(self._h))
+        self._check(rc)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise FFMPCError(f"ffmpc error {rc}: {self.lib.ffmpc_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.ffmpc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- host API: numpy in / numpy out, copies inside ------------------------------------------
+    def solve_host(self, inp: BatchInputs, max_iters: int, fixed_iters: bool = True, want=OUTPUT_NAMES, out: Optional[dict] = None) -> dict:
+        if out is None:
+            out = alloc_outputs(inp.B, self.N, self.nx, want)
+        s_in, s_out = inp.to_abi(), outputs_abi(out)
+        self._check(self.lib.ffmpc_solve_batch_host(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
+        return out
+
+    def solve_host_ptrs(self, s_in: _abi.BatchIn, s_out: _abi.BatchOut, max_iters: int, fixed_iters: bool = True):
+        """Same with pre-built pointer structs (e.g. pinned torch tensors), no allocation per call."""
+        self._check(self.lib.ffmpc_solve_batch_host(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
+
+    # ---- device API: torch CUDA tensors as buffers, stream-ordered, no sync ----------------------
+    def solve_device(self, t_in: dict, max_iters: int, fixed_iters: bool = True, t_out: Optional[dict] = None, stream=None) -> dict:
+        import torch
+
+        B = int(t_in["mode"].shape[0])
+        dev = t_in["x0"].device
+        if t_out is None:
+            shapes = dict(xs=(B, self.N + 1, self.nx), us=(B, self.N, 7), K=(B, self.N, 7, self.nx), k=(B, self.N, 7),
+                          cost=(B,), stop=(B,), gaps=(B, self.N + 1, self.nx), f_pred=(B, 2, 3), iters=(B,), ok=(B,))
+            t_out = {n: torch.empty(shapes[n], device=dev, dtype=torch.int32 if n in ("iters", "ok") else torch.float64)
+                     for n in OUTPUT_NAMES}
+        s_in = _abi.BatchIn()
+        s_in.B = B
+        for name in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref", "tau_ref", "xs_init", "us_init"):
+            t = t_in.get(name)
+            if t is not None:
+                assert t.is_cuda and t.is_contiguous(), name
+                assert t.dtype == (torch.int32 if name == "mode" else torch.float64), name
+            setattr(s_in, name, None if t is None else t.data_ptr())
+        s_out = _abi.BatchOut()
+        for name in OUTPUT_NAMES:
+            t = t_out.get(name)
+            setattr(s_out, name, None if t is None else t.data_ptr())
+        sp = None
+        if stream is not None:
+            sp = C.c_void_p(stream.cuda_stream)
+        self._check(self.lib.ffmpc_solve_batch(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out), sp))
+        return t_out
+
+    def sync(self):
+        self._check(self.lib.ffmpc_sync(self._h))
+
+    def last_timing(self):
+        ms, n = C.c_double(), C.c_int()
+        self._check(self.lib.ffmpc_last_timing(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    # ---- ActionModel.calc / calcDiff at arbitrary points (parity-test hook) ----------------------
+    def node_eval(self, inp: BatchInputs, inst, knot, x, u) -> dict:
+        inst = np.ascontiguousarray(inst, dtype=np.int32)
+        knot = np.ascontiguousarray(knot, dtype=np.int32)
+        M = inst.size
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(M, self.nx)
+        u = np.ascontiguousarray(u, dtype=np.float64).reshape(M, 7)
+        out = alloc_node_outputs(M, self.nx)
+        s_in, s_out = inp.to_abi(), node_outputs_abi(out)
+        self._check(self.lib.ffmpc_node_eval_host(self._h, C.byref(s_in), M, ptr(inst), ptr(knot), ptr(x), ptr(u), C.byref(s_out)))
+        return out

@@ -772,6 +772,7 @@ void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *
   double x[NJ], g[NJ], dx[NJ], xnew[NJ], Lff[NJ][NJ];
   for (int i = 0; i < n; ++i) x[i] = std::max(std::min(xinit[i], ub[i]), lb[i]);
   s.ok = true;
+  unsigned inv_mask = 0xffffffffu;
   for (int k = 0; k < cfg.boxqp_maxiter; ++k) {
     s.nf = s.ncl = 0;
     for (int i = 0; i < n; ++i) {
@@ -785,10 +786,17 @@ void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *
       if ((x[j] == lb[j] && g[j] > 0.0) || (x[j] == ub[j] && g[j] < 0.0)) s.clamped_idx[s.ncl++] = j;
       else s.free_idx[s.nf++] = j;
     }
+    unsigned mask = 0;
+    for (int i = 0; i < s.nf; ++i) mask |= 1u << s.free_idx[i];
     // convergence check
     if (gnorm <= cfg.boxqp_th_grad || s.nf == 0) {
-      if (k == 0) {
+      // crocoddyl::BoxQP factorises here only when k == 0 and otherwise returns the Hff_inv of the
+      // previous iteration; that is the same matrix unless the active set changed in the very last
+      // step, in which case upstream would hand back a stale block.  We re-factorise in that
+      // corner case so that Hff_inv always belongs to the returned free set.
+      if (k == 0 || mask != inv_mask) {
         if (!boxqp_free_inverse(H, cfg.boxqp_reg, s, Lff)) s.ok = false;
+        inv_mask = mask;
       }
       break;
     }
@@ -797,6 +805,7 @@ void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *
       s.ok = false;
       break;
     }
+    inv_mask = mask;
     double dxf[NJ];
     for (int i = 0; i < s.nf; ++i) {
       const int fi = s.free_idx[i];

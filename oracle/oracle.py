@@ -40,82 +40,8 @@ def lib():
     return _lib
 
 
-def _ptr(a):
-    return None if a is None else a.ctypes.data_as(C.c_void_p)
-
-
-def _f64(a, shape=None):
-    if a is None:
-        return None
-    a = np.ascontiguousarray(a, dtype=np.float64)
-    if shape is not None:
-        a = a.reshape(shape)
-    return a
-
-
-class BatchInputs:
-    """Host-side bundle matching ``ffmpc_batch_in``."""
-
-    def __init__(self, nx: int, N: int, mode, x0, p_ref, v_ref, x_reg_ref, tau_ref=None, xs_init=None, us_init=None):
-        self.nx, self.N = int(nx), int(N)
-        self.mode = np.ascontiguousarray(mode, dtype=np.int32).reshape(-1)
-        B = self.B = self.mode.size
-        self.x0 = _f64(x0, (B, nx))
-        self.p_ref = _f64(p_ref, (B, N + 1, 3))
-        self.v_ref = _f64(v_ref, (B, N + 1, 3))
-        self.x_reg_ref = _f64(x_reg_ref, (B, 14))
-        self.tau_ref = _f64(tau_ref, (B, 7))
-        self.xs_init = _f64(xs_init, (B, N + 1, nx))
-        self.us_init = _f64(us_init, (B, N, 7))
-
-    def to_abi(self) -> _abi.BatchIn:
-        s = _abi.BatchIn()
-        s.B = self.B
-        s.mode = _ptr(self.mode)
-        s.x0 = _ptr(self.x0)
-        s.p_ref = _ptr(self.p_ref)
-        s.v_ref = _ptr(self.v_ref)
-        s.x_reg_ref = _ptr(self.x_reg_ref)
-        s.tau_ref = _ptr(self.tau_ref)
-        s.xs_init = _ptr(self.xs_init)
-        s.us_init = _ptr(self.us_init)
-        return s
-
-    def slice(self, idx):
-        idx = np.asarray(idx)
-        g = lambda a: None if a is None else a[idx]
-        return BatchInputs(self.nx, self.N, self.mode[idx], self.x0[idx], self.p_ref[idx], self.v_ref[idx],
-                           self.x_reg_ref[idx], g(self.tau_ref), g(self.xs_init), g(self.us_init))
-
-
-def alloc_outputs(B: int, N: int, nx: int) -> dict:
-    return dict(
-        xs=np.zeros((B, N + 1, nx)), us=np.zeros((B, N, 7)), K=np.zeros((B, N, 7, nx)), k=np.zeros((B, N, 7)),
-        cost=np.zeros(B), stop=np.zeros(B), gaps=np.zeros((B, N + 1, nx)), f_pred=np.zeros((B, 2, 3)),
-        iters=np.zeros(B, dtype=np.int32), ok=np.zeros(B, dtype=np.int32),
-    )
-
-
-def outputs_abi(out: dict) -> _abi.BatchOut:
-    s = _abi.BatchOut()
-    for name, _ in _abi.BatchOut._fields_:
-        setattr(s, name, _ptr(out.get(name)))
-    return s
-
-
-def alloc_node_outputs(M: int, nx: int) -> dict:
-    return dict(
-        xnext=np.zeros((M, nx)), cost=np.zeros(M), force=np.zeros((M, 3)), Fx=np.zeros((M, nx, nx)),
-        Fu=np.zeros((M, nx, 7)), Lx=np.zeros((M, nx)), Lu=np.zeros((M, 7)), Lxx=np.zeros((M, nx, nx)),
-        Lxu=np.zeros((M, nx, 7)), Luu=np.zeros((M, 7, 7)),
-    )
-
-
-def node_outputs_abi(out: dict) -> _abi.NodeOut:
-    s = _abi.NodeOut()
-    for name, _ in _abi.NodeOut._fields_:
-        setattr(s, name, _ptr(out.get(name)))
-    return s
+from franka_force_feedback_mpc_b200.batch import (  # noqa: E402,F401  (shared host-side containers)
+    BatchInputs, alloc_node_outputs, alloc_outputs, node_outputs_abi, outputs_abi, f64 as _f64, ptr as _ptr)
 
 
 def _check(rc):
