@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""bench.py -- FDDP MPC solves/sec (fp64, batched) on 1..8 B200, one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch B] ...
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json config 4, the configuration the 1e5 solves/s/GPU target is quoted on):
+ForceFeedbackCrocoddylMPC OCP (nx=21, nu=7), normal_1d contact, horizon 50, dt_ocp 0.01, Box-FDDP with
+a FIXED 10 iterations (converged early exit disabled), cold start, synthetic x0 / reference
+trajectories: every GPU solves `--batch` (default 16384) instances made of the four sweep scenarios
+tilted_5 / tilted_10 / tilted_15 / actuation_uncertainty in equal parts (16384 x 4 GPUs = the 65536 of
+config 4).  One step = one batched solve of the whole per-GPU batch.  Instances are independent:
+ranks shard them, there is no collective on the solve path (weak scaling).
+
+Printed JSON line (rank 0): see the keys below; `value` = device-resident throughput (CUDA events on
+the solve stream), `e2e` = through the host-pointer C-ABI call with pinned host buffers, H2D of the
+inputs and D2H of xs/us/K/k/cost/iters/ok inside the timed region.
+
+`--impl reference` times the CPU restatement of the reference path (oracle/, -O3 AVX2 build, all host
+threads) on a bounded sample of the same workload.  The reference's own implementation is Crocoddyl /
+Pinocchio called from Python: not installed here or on the GPU box, so the oracle port
+is the CPU arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "fddp_mpc_solves_per_sec"
+UNIT = "solves/s"
+SCENARIOS = ("tilted_5", "tilted_10", "tilted_15", "actuation_uncertainty")
+
+# Algorithmic fp64 work, SURVEY.md section 8(d): dense-algebra operation counts of the reference algorithm
+# per knot (fma = 2), no credit for symmetry / sparsity.  FLOP per launch = per-knot figure x knots.
+F_DIFF = {0: 16000.0, 1: 20000.0, 3: 22000.0}   # action-model derivatives, by contact dimension
+F_CALC = {0: 5000.0, 1: 6500.0, 3: 6500.0}      # action-model calc (one rollout knot)
+F_EI = {21: 2000.0, 14: 1000.0}                  # gaps / expected-improvement terms per knot
+
+
+def f_bwd(nx: int, nu: int = 7) -> float:
+    return 4 * nx**3 + 6 * nx**2 * nu + 4 * nx * nu**2 + nu**3 / 3.0 + 6 * nx**2 + 4 * nx * nu + 4 * nu**2
+
+
+def flop_per_solve(nx: int, nc: int, N: int, iters: int, rollouts_per_iter: float = 1.0) -> float:
+    return iters * N * (F_DIFF[nc] + f_bwd(nx) + F_EI[nx] + rollouts_per_iter * F_CALC[nc])
+
+
+def io_bytes_per_solve(nx: int, N: int) -> int:
+    """Compulsory I/O of one solve: inputs x0, refs, warm start; outputs xs, us, K, k, scalars."""
+    n_in = (N + 1) * nx + N * 7 + (N + 1) * 6 + nx
+    n_out = (N + 1) * nx + N * 7 + N * 7 * nx + N * 7 + 4
+    return 8 * (n_in + n_out)
+
+
+# ------------------------------------------------------------------------------------------------
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=16384, help="instances per GPU per step")
+    ap.add_argument("--horizon", type=int, default=50)
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--variant", default="ff", choices=["ff", "classical"])
+    ap.add_argument("--contact-model", default="normal_1d", choices=["normal_1d", "point3d"])
+    ap.add_argument("--contact-fraction", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
+    return ap.parse_args()
+
+
+def make_problem(args, rank: int, B: int):
+    from franka_force_feedback_mpc_b200 import config, panda, synthetic
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+
+    ff = args.variant == "ff"
+    model = panda.default_model()
+    kw = dict(horizon=args.horizon, contact_model=args.contact_model, max_iters=args.iters)
+    cfgd = config.benchmark_ff_config(**kw) if ff else config.benchmark_classical_config(**kw)
+    cfg = config.to_abi(cfgd, model, panda.Q_NEUTRAL)
+    nx = 21 if ff else 14
+    parts = []
+    per = [B // len(SCENARIOS) + (1 if i < B % len(SCENARIOS) else 0) for i in range(len(SCENARIOS))]
+    for sc, n in zip(SCENARIOS, per):
+        if n == 0:
+            continue
+        seed = synthetic.SCENARIO_SEEDS[sc] + 1000 * 4 + 100000 * rank  # scenario seed + 1000 * config# (+ rank)
+        parts.append(synthetic.sample_instances(n, args.horizon, ff, seed=seed, contact_fraction=args.contact_fraction,
+                                                scenario=sc, model=model))
+    s = {k: np.concatenate([p[k] for p in parts], axis=0) for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+    inp = BatchInputs.from_samples(s, nx, args.horizon)
+    return cfg, model.to_abi(), inp, nx
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.rows, self.proc, self.device = [], None, device
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(args, cfg, model, inp, sample: int, nthreads: int) -> dict:
+    """The oracle port timed on the host cores, bounded sample of the same workload."""
+    from oracle import oracle as orc
+
+    lib, how = orc.timing_lib()
+    sub = inp.slice(np.arange(min(sample, inp.B)))
+    t0 = time.perf_counter()
+    orc.solve_batch(cfg, model, sub, args.iters, True, nthreads=nthreads, _use=lib)
+    dt = time.perf_counter() - t0
+    return {"value": sub.B / dt, "unit": UNIT, "cores": nthreads, "kind": "port",
+            "sample": f"{sub.B} instances of the same batch, {args.iters} fixed iterations, oracle/ffmpc_oracle.cpp ({how}), "
+                      f"{nthreads} threads over instances, {dt:.1f} s",
+            "note": "reference's own CPU path (Crocoddyl/Pinocchio via Python) is not installable on this box"}
+
+
+def run_reference(args, rank: int, world: int):
+    if rank != 0:
+        return
+    cfg, model, inp, nx = make_problem(args, 0, args.cpu_sample or 4 * (os.cpu_count() or 1))
+    from oracle import oracle as orc
+
+    lib, how = orc.timing_lib()
+    nthreads = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        orc.solve_batch(cfg, model, inp.slice(np.arange(min(nthreads, inp.B))), args.iters, True, nthreads=nthreads, _use=lib)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.solve_batch(cfg, model, inp, args.iters, True, nthreads=nthreads, _use=lib)
+    dt = time.perf_counter() - t0
+    val = inp.B * args.steps / dt
+    sample = (f"{inp.B} instances/step of the b200 arm's workload, oracle/ffmpc_oracle.cpp ({how}), {nthreads} threads over instances")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, inp.B, nx),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "CPU arm = from-scratch restatement of the reference algorithm (oracle/); Crocoddyl/Pinocchio themselves are "
+                "not installed on this box and cannot be (no network)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, B: int, nx: int) -> dict:
+    return {
+        "workload": f"{'ForceFeedback' if args.variant == 'ff' else 'Classical'}CrocoddylMPC OCP sweep (BASELINE config 4): "
+                    f"nx={nx} nu=7 {args.contact_model} contact, horizon {args.horizon}, dt_ocp 0.01, Box-FDDP, "
+                    f"{args.iters} fixed iterations, cold start, scenarios {'/'.join(SCENARIOS)}",
+        "batch_per_gpu": B, "horizon": args.horizon, "iters": args.iters, "nx": nx, "contact_fraction": args.contact_fraction,
+        "parallelism": f"instance-sharded x{args.gpus}, no collective on the solve path",
+        "l2": "per-step working set (node records + trajectories + gains) is GBs, far larger than the 126 MB L2",
+    }
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU path (use --impl reference for the CPU arm)")
+    import __graft_entry__ as ge
+    from franka_force_feedback_mpc_b200 import _abi, engine
+    from franka_force_feedback_mpc_b200.batch import OUTPUT_NAMES
+
+    if not os.path.exists(ge.LIB):
+        ge.build_cuda()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    B, N = args.batch, args.horizon
+    cfg, model, inp, nx = make_problem(args, rank, B)
+    nc = (3 if args.contact_model == "point3d" else 1) if args.contact_fraction > 0 else 0
+    eng = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=B)
+
+    # ---- device-resident inputs / outputs (torch tensors are only buffers) ----
+    t_in = {k: torch.from_numpy(getattr(inp, k)).to(dev) for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+    want = ("xs", "us", "K", "k", "cost", "stop", "iters", "ok", "f_pred")
+    shapes = dict(xs=(B, N + 1, nx), us=(B, N, 7), K=(B, N, 7, nx), k=(B, N, 7), cost=(B,), stop=(B,), gaps=(B, N + 1, nx),
+                  f_pred=(B, 2, 3), iters=(B,), ok=(B,))
+    t_out = {n: torch.empty(shapes[n], device=dev, dtype=torch.int32 if n in ("iters", "ok") else torch.float64) for n in want}
+    stream = torch.cuda.Stream(device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step_device():
+        eng.solve_device(t_in, args.iters, True, t_out=t_out, stream=stream)
+
+    eng.set_profiling(False)
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    eng.set_profiling(True)
+    fam_ms = {n: 0.0 for n in _abi.FAMILY_NAMES}
+    fam_launch = {n: 0 for n in _abi.FAMILY_NAMES}
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+        # (profile read-back happens after the timed region for the LAST step only; events are async)
+    with torch.cuda.stream(stream):
+        ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    prof = eng.get_profile()
+    for n, (ms, nl) in prof.items():
+        fam_ms[n], fam_launch[n] = ms, nl
+    eng.set_profiling(False)
+    clk = clocks.stop() if rank == 0 else None
+    t_ms = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_total = float(t_ms.item())
+    iters_out = t_out["iters"].cpu().numpy()
+    ok_dev = bool(np.all(iters_out == args.iters)) and bool(torch.isfinite(t_out["cost"]).all().item())
+
+    # ---- end to end through the host-pointer C-ABI call: pinned host buffers, H2D + D2H inside ----
+    h_in = {k: torch.from_numpy(getattr(inp, k)).pin_memory() for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+    e2e_want = ("xs", "us", "K", "k", "cost", "iters", "ok")
+    h_out = {n: torch.empty(shapes[n], dtype=torch.int32 if n in ("iters", "ok") else torch.float64).pin_memory() for n in e2e_want}
+    s_in = _abi.BatchIn()
+    s_in.B = B
+    for k, t in h_in.items():
+        setattr(s_in, k, t.data_ptr())
+    s_out = _abi.BatchOut()
+    for k, t in h_out.items():
+        setattr(s_out, k, t.data_ptr())
+    h2d = sum(t.numel() * t.element_size() for t in h_in.values())
+    d2h = sum(t.numel() * t.element_size() for t in h_out.values())
+    for _ in range(max(1, min(args.warmup, 2))):
+        eng.solve_host_ptrs(s_in, s_out, args.iters, True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.solve_host_ptrs(s_in, s_out, args.iters, True)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    t_e = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+    e2e_s = float(t_e.item())
+    e2e_ok = bool(np.isfinite(h_out["cost"].numpy()).all())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0 only: roofline, latency, CPU baseline ----
+    value = world * B * args.steps / (ms_total * 1e-3)
+    e2e_val = world * B * args.steps / e2e_s
+    peak_tf = engine.dfma_peak_tflops(local_rank)
+    knots = B * (N + 1)
+    fam_flop = {
+        "node_diff": knots * F_DIFF[nc] * args.iters,
+        "backward": B * N * f_bwd(nx) * args.iters,
+        "forward": knots * (F_CALC[nc] + F_EI[nx]) * args.iters,  # >= one rollout per iteration
+    }
+    dom = max(("node_diff", "backward", "forward"), key=lambda n: fam_ms[n])
+    dom_launches = max(1, fam_launch[dom])
+    achieved = fam_flop[dom] / (fam_ms[dom] * 1e-3) * 1e-12 if fam_ms[dom] > 0 else 0.0
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except (OSError, ValueError):
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    solve_ms = sum(fam_ms.values())
+    roofline = {
+        "bound": "fp64",  # neither "hbm" nor "tensor": the path is bound by the fp64 FMA pipe
+        "kernel": dom, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
+        "peak_source": "fp64 DFMA micro-benchmark run by this bench (ffmpc_dfma_peak); MEASURED_PEAKS.json has no fp64 entry",
+        "flop_per_launch": fam_flop[dom] / dom_launches, "ms_per_launch": fam_ms[dom] / dom_launches,
+        "traffic": None,
+        "kernel_ms_per_step": {n: fam_ms[n] for n in _abi.FAMILY_NAMES},
+        "kernel_share": {n: (fam_ms[n] / solve_ms if solve_ms else None) for n in _abi.FAMILY_NAMES},
+        "whole_solve": {
+            "flop_per_solve": flop_per_solve(nx, nc, N, args.iters),
+            "achieved_tflops": value / world * flop_per_solve(nx, nc, N, args.iters) * 1e-12,
+            "frac_of_fp64_peak": value / world * flop_per_solve(nx, nc, N, args.iters) * 1e-12 / peak_tf if peak_tf else None,
+            "io_bytes_per_solve": io_bytes_per_solve(nx, N),
+            "hbm_gbs_compulsory": value / world * io_bytes_per_solve(nx, N) * 1e-9,
+            "hbm_peak_gbs": hbm_peak, "hbm_peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+            "frac_of_hbm_peak": value / world * io_bytes_per_solve(nx, N) * 1e-9 / hbm_peak,
+        },
+    }
+
+    latency = None
+    if not args.no_latency:
+        one = inp.slice(np.arange(1))
+        eng1 = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=1)
+        o1 = None
+        lat = []
+        for i in range(60):
+            t0 = time.perf_counter()
+            o1 = eng1.solve_host(one, args.iters, True, want=("xs", "us", "K", "cost", "iters", "ok"), out=o1)
+            lat.append(time.perf_counter() - t0)
+        lat = np.array(lat[10:]) * 1e3
+        latency = {"p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)), "n": int(lat.size),
+                   "what": "B=1 solve through ffmpc_solve_batch_host (H2D + 10 fixed iterations + D2H), wall clock"}
+        eng1.close()
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        nthreads = os.cpu_count() or 1
+        cpu = cpu_baseline(args, cfg, model, inp, args.cpu_sample or 4 * nthreads, nthreads)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": workload_config(args, B, nx),
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ok": e2e_ok},
+        "gpu_launches": int(eng.last_timing()[1]) * args.steps,
+        "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "latency": latency, "all_iters_ran": ok_dev,
+    }
+    print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

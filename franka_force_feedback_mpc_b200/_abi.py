@@ -22,6 +22,9 @@ VARIANT_FF = 1
 MODE_FREE = 0
 MODE_CONTACT = 1
 
+NFAM = 4
+FAMILY_NAMES = ("other", "node_diff", "backward", "forward")
+
 c_double_p = C.POINTER(C.c_double)
 c_int_p = C.POINTER(C.c_int)
 
@@ -152,6 +155,9 @@ EXPORTED_SYMBOLS = [
     "ffmpc_solve_batch_host",
     "ffmpc_node_eval_host",
     "ffmpc_last_timing",
+    "ffmpc_set_profiling",
+    "ffmpc_get_profile",
+    "ffmpc_dfma_peak",
     "ffmpc_sync",
     "ffmpc_last_error",
     "ffmpc_version",

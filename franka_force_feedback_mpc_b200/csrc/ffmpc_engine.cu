@@ -58,6 +58,13 @@ struct ffmpc_handle {
   double last_ms = 0.0;
   int last_launches = 0;
   bool timing_valid = false;
+  // per-kernel-family profiling (ffmpc_set_profiling / ffmpc_get_profile)
+  bool profiling = false;
+  std::vector<cudaEvent_t> pev;      // event pool
+  std::vector<int> pfam;             // family of the interval that ENDS at event i+1
+  int pn = 0;                        // events recorded by the last solve
+  double fam_ms[FFMPC_NFAM] = {0, 0, 0, 0};
+  int fam_launches[FFMPC_NFAM] = {0, 0, 0, 0};
 };
 
 namespace {
@@ -81,6 +88,22 @@ int check_cfg(const ffmpc_config *c) {
   return FFMPC_OK;
 }
 
+// profiling: an event after every kernel family; the interval that ends at it is attributed to `fam`
+int mark(ffmpc_handle *h, int fam, int nlaunch) {
+  if (!h->profiling) return FFMPC_OK;
+  if (h->pn >= (int)h->pev.size()) {
+    cudaEvent_t e;
+    CU(cudaEventCreate(&e));
+    h->pev.push_back(e);
+    h->pfam.push_back(0);
+  }
+  h->pfam[h->pn] = fam;
+  if (fam >= 0) h->fam_launches[fam] += nlaunch;
+  CU(cudaEventRecord(h->pev[h->pn], h->stream));
+  h->pn++;
+  return FFMPC_OK;
+}
+
 int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
   Params P;
   P.mdl = h->mdl;
@@ -90,6 +113,9 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
   const int B = ws.B, N = ws.N;
   cudaStream_t st = h->stream;
   launches = 0;
+  h->pn = 0;
+  for (int f = 0; f < FFMPC_NFAM; ++f) { h->fam_ms[f] = 0.0; h->fam_launches[f] = 0; }
+  if (int e = mark(h, -1, 0)) return e;
   FFMPC_LAUNCH(k_build_perm, 1, 1024, 1025 * sizeof(int), st, ws);
   FFMPC_LAUNCH(k_init_state, (B + 127) / 128, 128, 0, st, P);
   {
@@ -98,10 +124,14 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
     FFMPC_LAUNCH(k_init_traj, grid, 256, 0, st, ws);
   }
   launches += 3;
+  if (int e = mark(h, FFMPC_FAM_OTHER, 3)) return e;
   for (int it = 0; it < max_iters; ++it) {
     launch_node_diff(P, st);
+    if (int e = mark(h, FFMPC_FAM_NODE_DIFF, 2)) return e;
     launch_backward(P, st);
+    if (int e = mark(h, FFMPC_FAM_BACKWARD, 1)) return e;
     launch_forward(P, it, st);
+    if (int e = mark(h, FFMPC_FAM_FORWARD, 2)) return e;
     launches += 5;
   }
   CU(cudaGetLastError());
@@ -116,6 +146,7 @@ int launch_export(ffmpc_handle *h, const ffmpc_batch_out *out, int &launches) {
   const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
   FFMPC_LAUNCH(k_export, grid, 256, 0, h->stream, h->ws, o);
   launches += 1;
+  if (int e = mark(h, FFMPC_FAM_OTHER, 1)) return e;
   CU(cudaGetLastError());
   return FFMPC_OK;
 }
@@ -249,6 +280,7 @@ void ffmpc_destroy(ffmpc_handle *h) {
   if (!h) return;
   cudaSetDevice(h->device);
   for (void *p : h->allocs) cudaFree(p);
+  for (cudaEvent_t e : h->pev) cudaEventDestroy(e);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -419,6 +451,32 @@ int ffmpc_last_timing(ffmpc_handle *h, double *kernel_ms, int *launches) {
   if (!h) return fail(FFMPC_ERR_ARG, "null handle");
   if (kernel_ms) *kernel_ms = h->timing_valid ? h->last_ms : -1.0;
   if (launches) *launches = h->last_launches;
+  return FFMPC_OK;
+}
+
+int ffmpc_set_profiling(ffmpc_handle *h, int on) {
+  if (!h) return fail(FFMPC_ERR_ARG, "null handle");
+  h->profiling = on != 0;
+  h->pn = 0;
+  return FFMPC_OK;
+}
+
+int ffmpc_get_profile(ffmpc_handle *h, double *ms, int *launches) {
+  if (!h) return fail(FFMPC_ERR_ARG, "null handle");
+  CU(cudaSetDevice(h->device));
+  for (int f = 0; f < FFMPC_NFAM; ++f) h->fam_ms[f] = 0.0;
+  if (h->pn > 1) {
+    CU(cudaEventSynchronize(h->pev[h->pn - 1]));
+    for (int i = 1; i < h->pn; ++i) {
+      float t = 0.f;
+      CU(cudaEventElapsedTime(&t, h->pev[i - 1], h->pev[i]));
+      if (h->pfam[i] >= 0) h->fam_ms[h->pfam[i]] += t;
+    }
+  }
+  for (int f = 0; f < FFMPC_NFAM; ++f) {
+    if (ms) ms[f] = h->fam_ms[f];
+    if (launches) launches[f] = h->fam_launches[f];
+  }
   return FFMPC_OK;
 }
 

@@ -34,6 +34,9 @@ def _declare(lib):
     lib.ffmpc_node_eval_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ffmpc_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.ffmpc_sync.argtypes = [C.c_void_p]
+    lib.ffmpc_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    lib.ffmpc_dfma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.ffmpc_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     return lib
 
 
@@ -51,6 +54,16 @@ def load_library(path: Optional[str] = None):
         _lib = _declare(C.CDLL(LIB_PATH))
         return _lib
     return _declare(C.CDLL(path))
+
+
+def dfma_peak_tflops(device: int = 0) -> float:
+    """Measured fp64 FMA-pipe peak of `device` in TFLOP/s (micro-benchmark inside the engine library)."""
+    lib = load_library()
+    tf, ms = C.c_double(), C.c_double()
+    rc = lib.ffmpc_dfma_peak(int(device), C.byref(tf), C.byref(ms))
+    if rc != 0:
+        raise FFMPCError(f"ffmpc_dfma_peak failed with code {rc}")
+    return tf.value
 
 
 class FFMPCEngine:
@@ -125,6 +138,16 @@ class FFMPCEngine:
 
     def sync(self):
         self._check(self.lib.ffmpc_sync(self._h))
+
+    def set_profiling(self, on: bool):
+        self._check(self.lib.ffmpc_set_profiling(self._h, int(bool(on))))
+
+    def get_profile(self) -> dict:
+        """{family: (device ms, kernel launches)} of the last solve (waits for it)."""
+        ms = (C.c_double * _abi.NFAM)()
+        nl = (C.c_int * _abi.NFAM)()
+        self._check(self.lib.ffmpc_get_profile(self._h, ms, nl))
+        return {name: (ms[i], nl[i]) for i, name in enumerate(_abi.FAMILY_NAMES)}
 
     def last_timing(self):
         ms, n = C.c_double(), C.c_int()

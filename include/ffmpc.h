@@ -195,6 +195,21 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
  * CUDA events on the solve stream, and the number of kernel launches it made. */
 int ffmpc_last_timing(ffmpc_handle *h, double *kernel_ms, int *launches);
 
+/* Per-kernel-family device times.  With profiling on, every solve records a CUDA event on the solve
+ * stream after each kernel family; ffmpc_get_profile waits for the last solve and returns, per family,
+ * the summed device time (ms) and the number of kernel launches.  Families: */
+#define FFMPC_FAM_OTHER 0     /* set-up (mode partition, state / trajectory init) + result export */
+#define FFMPC_FAM_NODE_DIFF 1 /* ShootingProblem.calc + calcDiff over all knots                    */
+#define FFMPC_FAM_BACKWARD 2  /* backwardPass + computeGains                                      */
+#define FFMPC_FAM_FORWARD 3   /* forwardPass / line search / acceptance                           */
+#define FFMPC_NFAM 4
+int ffmpc_set_profiling(ffmpc_handle *h, int on);
+int ffmpc_get_profile(ffmpc_handle *h, double *ms /*[FFMPC_NFAM]*/, int *launches /*[FFMPC_NFAM]*/);
+
+/* FP64 FMA-pipe micro-benchmark on `device` (8 independent DFMA chains per thread, no memory traffic):
+ * the measured roofline denominator of this compute-bound path (bench.py).  Best of 5 timed runs. */
+int ffmpc_dfma_peak(int device, double *tflops, double *ms /* nullable */);
+
 int ffmpc_sync(ffmpc_handle *h);
 const char *ffmpc_last_error(void);
 const char *ffmpc_version(void);

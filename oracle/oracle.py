@@ -17,7 +17,9 @@ from franka_force_feedback_mpc_b200 import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libffmpc_oracle.so")
+_FAST_PATH = os.path.join(_HERE, "libffmpc_oracle_fast.so")
 _lib = None
+_fast = None
 
 
 def build(force: bool = False) -> str:
@@ -26,8 +28,9 @@ def build(force: bool = False) -> str:
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.exists(p) and os.path.getmtime(p) > os.path.getmtime(_LIB_PATH) for p in (src, hdr)
     )
+    stale = stale or not os.path.exists(_FAST_PATH) or os.path.getmtime(_FAST_PATH) < os.path.getmtime(_LIB_PATH)
     if force or stale:
-        subprocess.check_call(["make", "-C", _HERE, "-B", "libffmpc_oracle.so"], stdout=subprocess.DEVNULL)
+        subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
     return _LIB_PATH
 
 
@@ -44,6 +47,31 @@ from franka_force_feedback_mpc_b200.batch import (  # noqa: E402,F401  (shared h
     BatchInputs, alloc_node_outputs, alloc_outputs, node_outputs_abi, outputs_abi, f64 as _f64, ptr as _ptr)
 
 
+def _cpu_has(*flags) -> bool:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    have = set(line.split(":", 1)[1].split())
+                    return all(fl in have for fl in flags)
+    except OSError:
+        pass
+    return False
+
+
+def timing_lib():
+    """Library for the TIMED cpu_baseline of bench.py: the -O3/AVX2/FMA build of the same source when the
+    host CPU supports it, else the plain build.  Returns (ctypes lib, description)."""
+    global _fast
+    if _fast is None:
+        if os.path.exists(_FAST_PATH) and _cpu_has("avx2", "fma"):
+            _fast = (C.CDLL(_FAST_PATH), "g++ -O3 -mavx2 -mfma")
+            _fast[0].ffmpc_oracle_last_error.restype = C.c_char_p
+        else:
+            _fast = (lib(), "g++ -O2")
+    return _fast
+
+
 def _check(rc):
     if rc != 0:
         raise RuntimeError(f"oracle error {rc}: {lib().ffmpc_oracle_last_error().decode()}")
@@ -56,10 +84,10 @@ def default_config(variant: int) -> _abi.Config:
 
 
 def solve_batch(cfg: _abi.Config, model: _abi.Model, inp: BatchInputs, max_iters: int, fixed_iters: bool = True,
-                nthreads: int = 1) -> dict:
+                nthreads: int = 1, _use=None) -> dict:
     out = alloc_outputs(inp.B, inp.N, inp.nx)
     s_in, s_out = inp.to_abi(), outputs_abi(out)
-    _check(lib().ffmpc_oracle_solve_batch(C.byref(cfg), C.byref(model), C.byref(s_in), int(max_iters),
+    _check((_use or lib()).ffmpc_oracle_solve_batch(C.byref(cfg), C.byref(model), C.byref(s_in), int(max_iters),
                                           int(bool(fixed_iters)), C.byref(s_out), int(nthreads)))
     return out
 
