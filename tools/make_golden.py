@@ -1,0 +1,179 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz by running the REFERENCE's own Python (imported from /root/reference,
+never copied) for the pieces of the hot path that are reference source rather than Crocoddyl:
+
+  lpf_golden.npz   _AugmentedLPFActionModel.calc / calcDiff  (src/mpc/crocoddyl_force_feedback.py:149-290)
+                   wrapped around an inner action model whose outputs come from the CPU oracle's
+                   classical knot (the inner Crocoddyl model itself is not installable here)
+  traj_golden.npz  make_approach_then_circle + the runners' 0.2 s hold wrapper
+                   (src/tasks/trajectories.py:8-93, src/run/run_classical.py:235-255)
+  misc_golden.npz  _ff_alpha_ocp / _policy_epsilon (crocoddyl_force_feedback.py:493-510)
+
+crocoddyl / pinocchio / example_robot_data are not installed: tiny stub modules are injected into
+sys.modules so that the reference files import; only pure-numpy reference code is executed.
+
+Run in the build container (needs /root/reference):   python tools/make_golden.py
+The fixtures are committed; the GPU box never runs this script.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import sys
+import types
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("FFMPC_REFERENCE", "/root/reference")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def install_stubs():
+    """Fake third-party modules: just enough surface for the reference files to import."""
+    croc = types.ModuleType("crocoddyl")
+
+    class StateVector:
+        def __init__(self, nx):
+            self.nx = int(nx)
+            self.ndx = int(nx)
+
+    class ActionModelAbstract:
+        def __init__(self, state, nu, nr=0):
+            self.state, self.nu, self.nr = state, int(nu), int(nr)
+
+    class ActionDataAbstract:
+        def __init__(self, model):
+            self.cost = 0.0
+            self.xnext = None
+
+    croc.StateVector = StateVector
+    croc.ActionModelAbstract = ActionModelAbstract
+    croc.ActionDataAbstract = ActionDataAbstract
+    pin = types.ModuleType("pinocchio")
+    erd = types.ModuleType("example_robot_data")
+    erd.load = lambda *a, **k: (_ for _ in ()).throw(RuntimeError("example_robot_data stub"))
+    mj = types.ModuleType("mujoco")
+    mj.viewer = types.ModuleType("mujoco.viewer")
+    for name, mod in (("crocoddyl", croc), ("pinocchio", pin), ("example_robot_data", erd), ("mujoco", mj),
+                      ("mujoco.viewer", mj.viewer)):
+        sys.modules.setdefault(name, mod)
+
+
+class OracleInner:
+    """Inner IntegratedActionModelEuler stand-in: outputs of the oracle's classical knot."""
+
+    def __init__(self, orc, cfg_inner, am, inp_inner, inst, knot):
+        self.orc, self.cfg, self.am, self.inp, self.inst, self.knot = orc, cfg_inner, am, inp_inner, inst, knot
+
+    def createData(self):
+        return types.SimpleNamespace()
+
+    def _eval(self, data, x, u):
+        o = self.orc.node_eval(self.cfg, self.am, self.inp, [self.inst], [self.knot], x[None], u[None])
+        for k in ("xnext", "cost", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"):
+            setattr(data, k, o[k][0])
+        data.cost = float(o["cost"][0])
+
+    def calc(self, data, x, u):
+        self._eval(data, np.asarray(x, float), np.asarray(u, float))
+
+    def calcDiff(self, data, x, u):
+        self._eval(data, np.asarray(x, float), np.asarray(u, float))
+
+
+def gen_lpf():
+    from ffmpc_cases import make_case
+    from franka_force_feedback_mpc_b200 import _abi
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+    from oracle import oracle as orc
+    from src.mpc.crocoddyl_force_feedback import _AugmentedLPFActionModel
+
+    N, B, seed = 12, 6, 101
+    out = {}
+    for tag, nc in (("nc1", 1), ("nc3", 3)):
+        cfg, am, inp = make_case(True, nc, B, N, seed, 0.67)
+        cfg_in = _abi.Config.from_buffer_copy(bytes(cfg))
+        cfg_in.variant = _abi.VARIANT_CLASSICAL
+        inp_in = BatchInputs(14, N, inp.mode, inp.x0[:, :14], inp.p_ref, inp.v_ref, inp.x_reg_ref)
+        rng = np.random.default_rng(seed + nc)
+        M = 24
+        inst = rng.integers(0, B, M).astype(np.int32)
+        knot = rng.integers(0, N, M).astype(np.int32)  # running knots (terminal quirk a16 is tested separately)
+        x = inp.x0[inst] + rng.normal(0.0, 0.05, (M, 21))
+        w = inp.x0[inst][:, 14:] + rng.normal(0.0, 3.0, (M, 7))
+        w[::3] *= 4.0  # push some controls over the soft limit so that branch is exercised
+        lim = np.array([cfg.tau_limits[i] for i in range(7)])
+        ywts = np.array([cfg.y_reg_weights[i] for i in range(21)])
+        res = {k: [] for k in ("xnext", "cost", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")}
+        for m in range(M):
+            inner = OracleInner(orc, cfg_in, am, inp_in, int(inst[m]), int(knot[m]))
+            model = _AugmentedLPFActionModel(inner, 14, 7, cfg.ff_alpha, cfg.w_w, cfg.w_w_soft_limits, lim,
+                                             cfg.tau_soft_limit_margin, cfg.w_y, inp.x0[inst[m]], ywts)
+            d = types.SimpleNamespace(inner=inner.createData())
+            model.calc(d, x[m], w[m])
+            model.calcDiff(d, x[m], w[m])
+            for k in res:
+                res[k].append(np.array(getattr(d, k), dtype=float))
+        for k, v in res.items():
+            out[f"{tag}_{k}"] = np.stack(v)
+        out[f"{tag}_x"], out[f"{tag}_w"], out[f"{tag}_inst"], out[f"{tag}_knot"] = x, w, inst, knot
+    out["N"], out["B"], out["seed"], out["contact_fraction"] = N, B, seed, 0.67
+    np.savez_compressed(os.path.join(GOLD, "lpf_golden.npz"), **out)
+    print("lpf_golden.npz", {k: np.shape(v) for k, v in out.items() if k.startswith("nc1")})
+
+
+def gen_traj():
+    from franka_force_feedback_mpc_b200 import panda
+    from franka_force_feedback_mpc_b200.panda import R_MJ_FROM_PIN
+    from src.tasks.trajectories import make_approach_then_circle
+
+    model = panda.default_model()
+    p_pin, _ = model.fk(panda.Q_NEUTRAL)
+    ee_start = R_MJ_FROM_PIN @ p_pin
+    base = make_approach_then_circle(center=np.array([-0.5, 0.0, 0.342]), radius=0.10, omega=1.5, z_pre=0.392,
+                                     z_contact=0.342, t_approach=0.55, ee_start=ee_start.copy(), t_pre=0.25)
+    t_c, t_hold = 0.25 + 0.55, 0.2
+
+    def traj(t):  # the runners' hold wrapper, run_classical.py:249-255 (closure in the runner: restated in 5 lines)
+        p, v, s = base(t)
+        if s and float(t) < t_c + t_hold:
+            ph, _, _ = base(t_c)
+            return np.asarray(ph, float), np.zeros(3), True
+        return p, v, s
+
+    ts = np.concatenate([np.linspace(0.0, 1.2, 241), np.array([0.25, 0.8, 0.8 - 1e-9, 1.0, 1.0 - 1e-12]), np.linspace(1.2, 20.0, 95)])
+    P, V, S = zip(*(traj(float(t)) for t in ts))
+    np.savez_compressed(os.path.join(GOLD, "traj_golden.npz"), t=ts, p=np.stack(P), v=np.stack(V), surface=np.array(S),
+                        ee_start=ee_start)
+    print("traj_golden.npz", len(ts))
+
+
+def gen_misc():
+    from src.mpc.crocoddyl_force_feedback import ForceFeedbackCrocoddylMPC as FF
+
+    rows = []
+    for fc in (5.0, 18.0, 25.0, 60.0):
+        for dt_ocp, dt in ((0.01, 0.005), (0.02, 0.005), (0.01, 0.01)):
+            fake = types.SimpleNamespace(cfg=types.SimpleNamespace(ff_cutoff_hz=fc, dt_ocp=dt_ocp, dt=dt, ff_alpha_override=None),
+                                         sim=types.SimpleNamespace(dt=dt), _dt_ocp=dt_ocp)
+            rows.append((fc, dt_ocp, dt, FF._ff_alpha_ocp(fake), FF._ff_alpha_ctrl(fake), FF._policy_epsilon(fake)))
+    np.savez_compressed(os.path.join(GOLD, "misc_golden.npz"), alpha_rows=np.array(rows))
+    print("misc_golden.npz", len(rows))
+
+
+def main():
+    if not os.path.isdir(REF):
+        raise SystemExit(f"{REF} not found: the golden fixtures can only be regenerated where the reference is mounted")
+    os.makedirs(GOLD, exist_ok=True)
+    install_stubs()
+    sys.path.insert(0, REF)
+    gen_lpf()
+    gen_traj()
+    gen_misc()
+
+
+if __name__ == "__main__":
+    main()
