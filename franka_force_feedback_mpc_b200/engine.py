@@ -35,7 +35,8 @@ def _declare(lib):
     lib.ffmpc_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.ffmpc_sync.argtypes = [C.c_void_p]
     lib.ffmpc_set_profiling.argtypes = [C.c_void_p, C.c_int]
-    lib.ffmpc_dfma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    if hasattr(lib, "ffmpc_dfma_peak"):  # absent from the test-only host emulator build
+        lib.ffmpc_dfma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.ffmpc_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     return lib
 
