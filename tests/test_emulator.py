@@ -1,0 +1,105 @@
+"""CPU CI for the CUDA sources: tests/host_emul compiles the SAME kernel sources (ffmpc_kernels.cuh /
+ffmpc_node.cuh / ffmpc_engine.cu) against a fiber-based CUDA emulator (grid/block/warp shuffles/shared
+memory) and this file compares that build with the oracle -- so a logic error in a kernel shows up in
+`-m "not gpu"` before any GPU time is spent.  The emulator library is test-only and never shipped; the
+GPU parity tests proper are tests/test_gpu_parity.py."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from ffmpc_cases import make_case, rel_err
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU_DIR = os.path.join(HERE, "host_emul")
+NODE_KEYS = ("xnext", "cost", "force", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    subprocess.check_call(["make", "-C", EMU_DIR, "all"], stdout=subprocess.DEVNULL)
+    from franka_force_feedback_mpc_b200 import engine
+
+    lib = engine.load_library(os.path.join(EMU_DIR, "libffmpc_emu.so"))
+    assert b"EMULATION" in lib.ffmpc_version()
+    return lib
+
+
+def _engine(emu, cfg, am, B):
+    from franka_force_feedback_mpc_b200 import engine
+
+    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B, _lib=emu)
+
+
+@pytest.mark.parametrize("ff", [False, True])
+@pytest.mark.parametrize("nc,cf", [(1, 1.0), (1, 0.0), (3, 0.5)])
+def test_emulated_node_kernels_match_oracle(emu, orc, ff, nc, cf):
+    B, N = 6, 8
+    cfg, am, inp = make_case(ff, nc, B, N, 31, cf)
+    rng = np.random.default_rng(7)
+    inst = np.repeat(np.arange(B), 3).astype(np.int32)
+    knot = np.tile([0, 3, N], B).astype(np.int32)
+    x = inp.x0[inst] + rng.normal(0, 0.02, (inst.size, inp.nx))
+    u = rng.normal(0, 3.0, (inst.size, 7)) + (inp.x0[inst][:, 14:21] if ff else 0.0)
+    u[::5] *= 40.0  # some controls beyond the soft limits
+    eng = _engine(emu, cfg, am, B)
+    out = eng.node_eval(inp, inst, knot, x, u)
+    eng.close()
+    ref = orc.node_eval(cfg, am, inp, inst, knot, x, u)
+    contact = inp.mode[inst] == 1
+    for k in NODE_KEYS:
+        a, b = out[k], ref[k]
+        if k == "force":
+            a, b = a[contact], b[contact]
+            if a.size == 0:
+                continue
+        assert rel_err(a, b) < 1e-10, k
+
+
+@pytest.mark.parametrize("ff,nc,cf,box", [(False, 1, 1.0, 1), (False, 1, 0.0, 1), (True, 1, 0.5, 1), (True, 3, 1.0, 1), (True, 1, 1.0, 0)])
+def test_emulated_solver_matches_oracle(emu, orc, ff, nc, cf, box):
+    B, N, iters = 5, 12, 6
+    cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
+    cfg.use_box_fddp = box
+    eng = _engine(emu, cfg, am, B)
+    out = eng.solve_host(inp, iters, True)
+    eng.close()
+    ref = orc.solve_batch(cfg, am, inp, iters, True)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["ok"], ref["ok"])
+    for k in ("xs", "us", "K", "k", "cost", "stop"):
+        assert rel_err(out[k], ref[k]) < 1e-6, k
+    assert np.abs(out["gaps"] - ref["gaps"]).max() < 1e-9
+    c = inp.mode == 1
+    if c.any():
+        assert rel_err(out["f_pred"][c], ref["f_pred"][c]) < 1e-6
+
+
+def test_emulated_early_exit_and_warm_start(emu, orc):
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+
+    B, N = 4, 10
+    cfg, am, inp = make_case(True, 1, B, N, 17, 1.0)
+    eng = _engine(emu, cfg, am, B)
+    a = eng.solve_host(inp, 50, False)
+    ra = orc.solve_batch(cfg, am, inp, 50, False)
+    assert np.array_equal(a["iters"], ra["iters"]) and np.array_equal(a["ok"], ra["ok"])
+    assert np.all(a["ok"] == 1) and np.all(a["stop"] < cfg.th_stop)
+    warm = BatchInputs(inp.nx, N, inp.mode, inp.x0, inp.p_ref, inp.v_ref, inp.x_reg_ref, xs_init=a["xs"], us_init=a["us"],
+                       tau_ref=np.zeros((B, 7)))
+    b = eng.solve_host(warm, 3, True)
+    rb = orc.solve_batch(cfg, am, warm, 3, True)
+    eng.close()
+    for k in ("xs", "us", "cost"):
+        assert rel_err(b[k], rb[k]) < 1e-7, k
+
+
+def test_emulated_capacity_and_argument_errors(emu):
+    from franka_force_feedback_mpc_b200 import engine
+
+    cfg, am, inp = make_case(False, 1, 4, 6, 1, 1.0)
+    eng = _engine(emu, cfg, am, 2)
+    with pytest.raises(engine.FFMPCError) as e:
+        eng.solve_host(inp, 2, True)
+    assert "max_batch" in str(e.value)
+    eng.close()

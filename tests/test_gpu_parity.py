@@ -1,0 +1,215 @@
+"""GPU parity tests proper (`-m gpu`): the CUDA engine, called through the C ABI of include/ffmpc.h
+(ffmpc_solve_batch_host / ffmpc_solve_batch / ffmpc_node_eval_host), against the CPU oracle on the same
+seeded inputs, plus size-independent properties at BASELINE.json's full sizes.
+
+Tolerances (fp64 everywhere; north_star: gains K/k, cost, gaps within 1e-8 relative at a fixed iteration count):
+  * one action-model evaluation (calc + calcDiff):         1e-10 relative to the largest entry of each block
+  * one FDDP iteration (K, k, cost, xs, us; gaps absolute): 1e-8
+  * 10 fixed iterations:                                    >= 90 % of the instances within 1e-8 and every instance
+    within 1e-5 -- the oracle differentiates by forward-mode AD, the kernels by analytic recursions, so the two
+    differ by rounding (1e-16) per knot and ten nonlinear Newton-type iterations amplify that on ill-conditioned
+    instances; accept/reject decisions (iters, ok) must still agree exactly.
+"""
+import numpy as np
+import pytest
+
+from ffmpc_cases import make_case, rel_err
+
+pytestmark = pytest.mark.gpu
+NODE_KEYS = ("xnext", "cost", "force", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+VARIANTS = [(False, 1, 1.0), (False, 1, 0.0), (False, 3, 0.5), (True, 1, 1.0), (True, 1, 0.0), (True, 3, 0.5)]
+
+
+def _eng(cfg, am, B):
+    from franka_force_feedback_mpc_b200 import engine
+
+    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B)
+
+
+def _inst_rel(a, b):
+    """per-instance max-abs error relative to that instance's largest reference entry"""
+    a = np.asarray(a, float).reshape(a.shape[0], -1)
+    b = np.asarray(b, float).reshape(b.shape[0], -1)
+    return np.abs(a - b).max(axis=1) / np.maximum(np.abs(b).max(axis=1), 1e-300)
+
+
+@pytest.mark.parametrize("ff,nc,cf", VARIANTS)
+def test_node_calc_and_calcdiff_match_oracle(built, orc, ff, nc, cf):
+    B, N = 64, 50
+    cfg, am, inp = make_case(ff, nc, B, N, 31, cf)
+    rng = np.random.default_rng(7)
+    inst = np.repeat(np.arange(B), 4).astype(np.int32)
+    knot = np.tile([0, 7, N - 1, N], B).astype(np.int32)
+    x = inp.x0[inst] + rng.normal(0, 0.03, (inst.size, inp.nx))
+    u = rng.normal(0, 3.0, (inst.size, 7)) + (inp.x0[inst][:, 14:21] if ff else 0.0)
+    u[::5] *= 40.0  # beyond the soft torque limits
+    eng = _eng(cfg, am, B)
+    out = eng.node_eval(inp, inst, knot, x, u)
+    eng.close()
+    ref = orc.node_eval(cfg, am, inp, inst, knot, x, u)
+    contact = inp.mode[inst] == 1
+    for k in NODE_KEYS:
+        a, b = out[k], ref[k]
+        if k == "force":
+            a, b = a[contact], b[contact]
+            if a.size == 0:
+                continue
+        assert rel_err(a, b) < 1e-10, k
+
+
+@pytest.mark.parametrize("ff,nc,cf", VARIANTS)
+def test_one_iteration_gains_cost_gaps(built, orc, ff, nc, cf):
+    B, N = 48, 50
+    cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
+    eng = _eng(cfg, am, B)
+    out = eng.solve_host(inp, 1, True)
+    eng.close()
+    ref = orc.solve_batch(cfg, am, inp, 1, True, nthreads=8)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["ok"], ref["ok"])
+    for k in ("K", "k", "cost", "xs", "us", "stop"):
+        assert _inst_rel(out[k], ref[k]).max() < 1e-8, k
+    assert np.abs(out["gaps"] - ref["gaps"]).max() < 1e-8 * max(1.0, np.abs(ref["gaps"]).max())
+
+
+@pytest.mark.parametrize("ff,nc,cf", VARIANTS)
+def test_ten_fixed_iterations_match_oracle(built, orc, ff, nc, cf):
+    B, N, iters = 64, 50, 10
+    cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
+    eng = _eng(cfg, am, B)
+    out = eng.solve_host(inp, iters, True)
+    eng.close()
+    ref = orc.solve_batch(cfg, am, inp, iters, True, nthreads=8)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["ok"], ref["ok"])
+    for k in ("K", "k", "cost", "xs", "us"):
+        e = _inst_rel(out[k], ref[k])
+        assert np.mean(e < 1e-8) >= 0.9, (k, np.sort(e)[-8:])
+        assert e.max() < 1e-5, (k, e.max())
+    assert np.abs(out["gaps"] - ref["gaps"]).max() < 1e-8 * max(1.0, np.abs(ref["gaps"]).max())
+    c = inp.mode == 1
+    if c.any():
+        assert _inst_rel(out["f_pred"][c], ref["f_pred"][c]).max() < 1e-5
+    assert np.isnan(out["f_pred"][~c]).all()
+
+
+def test_plain_fddp_and_early_exit(built, orc):
+    """use_box_fddp = 0 (`solver="fddp"`, crocoddyl_classical.py:442-445) and the converged early exit."""
+    B, N = 32, 30
+    cfg, am, inp = make_case(True, 1, B, N, 17, 0.75)
+    cfg.use_box_fddp = 0
+    eng = _eng(cfg, am, B)
+    a = eng.solve_host(inp, 6, True)
+    ra = orc.solve_batch(cfg, am, inp, 6, True, nthreads=8)
+    for k in ("xs", "us", "K", "cost"):
+        assert _inst_rel(a[k], ra[k]).max() < 1e-5, k
+    eng.close()
+    cfg.use_box_fddp = 1
+    eng = _eng(cfg, am, B)
+    b = eng.solve_host(inp, 100, False)
+    rb = orc.solve_batch(cfg, am, inp, 100, False, nthreads=8)
+    eng.close()
+    assert np.array_equal(b["ok"], rb["ok"]) and np.all(b["ok"] == 1)
+    assert np.all(b["stop"] < cfg.th_stop)
+    assert np.mean(b["iters"] == rb["iters"]) >= 0.9  # the stop measure sits at the threshold for a few instances
+    assert _inst_rel(b["cost"], rb["cost"]).max() < 1e-6
+
+
+def test_warm_start_inputs_and_given_tau_ref(built, orc):
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+
+    B, N = 32, 40
+    cfg, am, inp = make_case(False, 1, B, N, 23, 1.0)
+    eng = _eng(cfg, am, B)
+    a = eng.solve_host(inp, 4, True)
+    # `_shift_guess` (crocoddyl_classical.py:733-757): xs = [x0] + xs_prev[1:], us = us_prev[1:] + [us_prev[-1]]
+    xs_init = a["xs"].copy(); xs_init[:, 0] = inp.x0
+    us_init = np.concatenate([a["us"][:, 1:], a["us"][:, -1:]], axis=1)
+    tau_ref = np.random.default_rng(0).normal(0, 1.0, (B, 7))
+    warm = BatchInputs(14, N, inp.mode, inp.x0, inp.p_ref, inp.v_ref, inp.x_reg_ref, tau_ref=tau_ref, xs_init=xs_init, us_init=us_init)
+    b = eng.solve_host(warm, 3, True)
+    eng.close()
+    rb = orc.solve_batch(cfg, am, warm, 3, True, nthreads=8)
+    assert np.array_equal(b["iters"], rb["iters"])
+    for k in ("xs", "us", "K", "k", "cost"):
+        assert _inst_rel(b[k], rb[k]).max() < 1e-6, k
+
+
+def test_device_pointer_api_equals_host_api(built):
+    """ffmpc_solve_batch (device pointers from torch tensors, caller's stream) == ffmpc_solve_batch_host, bit for bit."""
+    import torch
+
+    B, N = 128, 50
+    cfg, am, inp = make_case(True, 1, B, N, 3, 0.75)
+    eng = _eng(cfg, am, B)
+    h = eng.solve_host(inp, 5, True)
+    dev = torch.device("cuda", 0)
+    t_in = {k: torch.from_numpy(getattr(inp, k)).to(dev) for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+    st = torch.cuda.Stream(device=dev)
+    d = eng.solve_device(t_in, 5, True, stream=st)
+    st.synchronize()
+    eng.close()
+    for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok"):
+        assert np.array_equal(d[k].cpu().numpy(), h[k]), k
+
+
+def test_ragged_and_edge_batches(built, orc):
+    """B = 1, a batch that is not a multiple of any block size, all-free / all-contact / mixed modes."""
+    N = 20
+    for B, cf in ((1, 1.0), (1, 0.0), (37, 0.5), (129, 1.0)):
+        cfg, am, inp = make_case(True, 1, B, N, 11 + B, cf)
+        eng = _eng(cfg, am, max(B, 200))  # handle larger than the batch
+        out = eng.solve_host(inp, 3, True)
+        eng.close()
+        ref = orc.solve_batch(cfg, am, inp, 3, True, nthreads=8)
+        assert np.array_equal(out["iters"], ref["iters"])
+        assert _inst_rel(out["cost"], ref["cost"]).max() < 1e-8
+        assert _inst_rel(out["K"], ref["K"]).max() < 1e-6
+
+
+def test_errors_through_the_abi(built):
+    from franka_force_feedback_mpc_b200 import engine
+
+    cfg, am, inp = make_case(False, 1, 8, 10, 1, 1.0)
+    eng = _eng(cfg, am, 4)
+    with pytest.raises(engine.FFMPCError) as e:
+        eng.solve_host(inp, 2, True)
+    assert "max_batch" in str(e.value)
+    eng.close()
+    with pytest.raises(engine.FFMPCError):
+        engine.FFMPCEngine(cfg, am, device=99, max_batch=4)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json full sizes: properties that need no oracle run
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ff,nc,B,iters,cf", [(False, 1, 4096, 10, 1.0),      # config 3
+                                               (True, 1, 16384, 10, 1.0),      # one GPU's share of config 4
+                                               (True, 3, 4096, 20, 0.75)])     # config 5 (reduced batch)
+def test_full_size_properties(built, orc, ff, nc, B, iters, cf):
+    N = 50
+    cfg, am, inp = make_case(ff, nc, B, N, 1000 * 3 + 11, cf, scenario="actuation_uncertainty" if ff else "flat")
+    eng = _eng(cfg, am, B)
+    want = ("xs", "us", "cost", "gaps", "iters", "ok", "stop")
+    a = eng.solve_host(inp, iters, True, want=want)
+    # determinism: the same call twice is bit-identical
+    a2 = eng.solve_host(inp, iters, True, want=want)
+    for k in want:
+        assert np.array_equal(a[k], a2[k]), k
+    # permutation equivariance: instances are independent, results do not depend on batch position or neighbours
+    perm = np.random.default_rng(0).permutation(B)
+    p = eng.solve_host(inp.slice(perm), iters, True, want=want)
+    for k in ("xs", "us", "cost"):
+        assert np.array_equal(p[k], a[k][perm]), k
+    # fewer iterations never give a lower cost (monotone descent of accepted steps)
+    h = eng.solve_host(inp, iters // 2, True, want=want)
+    eng.close()
+    assert np.all(a["cost"] <= h["cost"] + 1e-9 * np.abs(h["cost"]))
+    assert np.all(np.isfinite(a["cost"])) and np.array_equal(a["iters"], np.full(B, iters))
+    assert np.all(np.abs(a["us"]) <= np.array(cfg.tau_limits) + 1e-12)
+    assert np.allclose(a["xs"][:, 0], inp.x0, atol=0, rtol=0) or np.abs(a["gaps"][:, 0]).max() > 0
+    closed = np.abs(a["gaps"]).reshape(B, -1).max(axis=1) < 1e-9
+    assert closed.mean() > 0.99
+    # a random sample of the full batch agrees with the oracle
+    idx = np.random.default_rng(1).choice(B, 24, replace=False)
+    ref = orc.solve_batch(cfg, am, inp.slice(idx), iters, True, nthreads=8)
+    e = _inst_rel(a["cost"][idx], ref["cost"])
+    assert np.mean(e < 1e-8) >= 0.9 and e.max() < 1e-5
