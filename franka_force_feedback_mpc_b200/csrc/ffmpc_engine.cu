@@ -7,6 +7,7 @@
 // run the kernel sources in CPU CI; that build is a separate test-only library.)
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -42,6 +43,7 @@ struct ffmpc_handle {
   int device = 0;
   int max_batch = 0;
   int N = 0, nx = 0;
+  int lgA_max = 0;  // log2 of the line-search lanes per instance the trajectory slots were sized for
   ffmpc_config cfg;
   ffmpc_model mdl;
   cudaStream_t stream = nullptr;
@@ -75,6 +77,24 @@ template <class T> int dalloc(ffmpc_handle *h, T **p, size_t count) {
   h->allocs.push_back(q);
   *p = (T *)q;
   return FFMPC_OK;
+}
+
+// Lanes per instance of the parallel line search (k_forward).  The rollout is sequential in the horizon, so a
+// small batch cannot fill the GPU with one thread per instance: spread the step lengths over lanes until about
+// 64k threads exist; large batches keep 2 lanes (less speculative work, still no 10-deep divergence).
+// FFMPC_FWD_LANES overrides (1, 2, 4, ... 32) for experiments.
+int fwd_lanes_log2(int batch, int n_alphas) {
+  int lg;
+  if (batch >= 32768) lg = 1;
+  else if (batch >= 8192) lg = 2;
+  else if (batch >= 2048) lg = 3;
+  else lg = 4;
+  if (const char *e = getenv("FFMPC_FWD_LANES")) {
+    const int a = atoi(e);
+    if (a >= 1 && a <= 32) { lg = 0; while ((1 << lg) < a) ++lg; }
+  }
+  while (lg > 0 && (1 << (lg - 1)) >= n_alphas) --lg;  // never more lanes than step lengths (rounded up to 2^k)
+  return lg;
 }
 
 int check_cfg(const ffmpc_config *c) {
@@ -130,7 +150,7 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
     if (int e = mark(h, FFMPC_FAM_NODE_DIFF, 2)) return e;
     launch_backward(P, st);
     if (int e = mark(h, FFMPC_FAM_BACKWARD, 1)) return e;
-    launch_forward(P, it, st);
+    launch_forward(P, it, std::min(h->lgA_max, fwd_lanes_log2(B, h->cfg.n_alphas)), st);
     if (int e = mark(h, FFMPC_FAM_FORWARD, 2)) return e;
     launches += 5;
   }
@@ -251,8 +271,11 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   DA(ws.tau_ref, B * NJ);
   DA(ws.perm, B);
   DA(ws.counts, 2);
-  DA(ws.xs, 2 * B * (N + 1) * nx);
-  DA(ws.us, 2 * B * N * NJ);
+  // parallel line search: A = 2^lgA lanes per instance, each with its own trial slot (see k_forward)
+  h->lgA_max = fwd_lanes_log2(max_batch, cfg->n_alphas);
+  ws.nslots = 1 + (1 << h->lgA_max);
+  DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
+  DA(ws.us, (size_t)ws.nslots * B * N * NJ);
   DA(ws.fs, B * (N + 1) * nx);
   DA(ws.rec, B * (N + 1) * REC_SIZE);
   DA(ws.ncost, B * (N + 1));

@@ -24,8 +24,9 @@ struct Workspace {
   double *tau_ref;  // [B,7]
   int *perm;        // [B] instance ids, free-mode first then contact-mode
   int *counts;      // [2] = {#free, #contact}
-  double *xs;       // [2,B,N+1,nx]  parity double buffer (accepted / trial)
-  double *us;       // [2,B,N,7]
+  int nslots;       // trajectory slots per instance = 1 (accepted) + lanes of the parallel line search
+  double *xs;       // [nslots,B,N+1,nx]  slot cur[b] = accepted candidate, the others = trial buffers
+  double *us;       // [nslots,B,N,7]
   double *fs;       // [B,N+1,nx]
   double *rec;      // [B,N+1,REC_SIZE]
   double *ncost;    // [B,N+1]
@@ -222,180 +223,180 @@ __global__ void __launch_bounds__(128) k_node_diff(const __grid_constant__ Param
 }
 
 // ------------------------------------------------------------------------------------------------
-// 7x7 helpers used redundantly by all lanes of the backward warp (uniform control flow)
+// Warp-cooperative 7x7 algebra of the backward pass.  Lane i < 7 owns ROW i of the symmetric 7x7
+// matrix (7 registers); the other lanes execute the same instructions on dummy rows (SIMT: a
+// warp-wide instruction costs the same with 7 or 32 useful lanes, but 7 registers instead of 49
+// per lane is what lets 16 warps live on an SM).  Every result that steers control flow is made
+// warp-uniform with a broadcast from lane 0.
 // ------------------------------------------------------------------------------------------------
-// Cholesky of the lower triangle of A; `mask` bit i clear -> row/col i replaced by identity (BoxQP free set).
-// Returns false on a non-positive pivot (Eigen::LLT NumericalIssue).  Li = L^-1 (lower).
-FFMPC_DEV bool chol7(const double A[NJ][NJ], unsigned mask, double L[NJ][NJ], double Li[NJ][NJ]) {
+FFMPC_DEV double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+FFMPC_DEV double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// sum / max over lanes 0..7 (callers make lane 7 contribute the neutral element), broadcast to the warp
+FFMPC_DEV double sum8(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return shfl_d(v, 0);
+}
+FFMPC_DEV double max8(double v) {
+  v = fmax(v, __shfl_xor_sync(0xffffffffu, v, 1));
+  v = fmax(v, __shfl_xor_sync(0xffffffffu, v, 2));
+  v = fmax(v, __shfl_xor_sync(0xffffffffu, v, 4));
+  return shfl_d(v, 0);
+}
+// every lane receives the 7-vector whose component j lives on lane j
+FFMPC_DEV void gather7(double mine, double *out) {
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) out[j] = shfl_d(mine, j);
+}
+
+// Cholesky of the 7x7 SPD matrix whose row `lane` is a[0..6]; rows / columns outside `mask` are replaced
+// by identity (BoxQP free set).  On exit a[j], j <= lane, is L[lane][j] and dinv = 1 / L[lane][lane].
+// Returns false (uniformly) on a non-positive pivot (Eigen::LLT NumericalIssue).
+FFMPC_DEV bool dist_chol7(double *a, unsigned mask, int lane, double &dinv) {
   bool ok = true;
+  const bool fi = (mask >> lane) & 1u;
 #pragma unroll
   for (int j = 0; j < NJ; ++j) {
     const bool fj = (mask >> j) & 1u;
-    double s = fj ? A[j][j] : 1.0;
+    if (!(fi && fj)) a[j] = (lane == j) ? 1.0 : 0.0;
+  }
+  dinv = 1.0;
 #pragma unroll
-    for (int k = 0; k < j; ++k) s -= L[j][k] * L[j][k];
-    if (!(s > 0.0)) ok = false;
-    const double l = sqrt(s);
-    const double il = 1.0 / l;
-    L[j][j] = l;
-    Li[j][j] = il;
+  for (int j = 0; j < NJ; ++j) {
+    const double d = shfl_d(a[j], j);
+    if (!(d > 0.0)) ok = false;
+    const double r = rsqrt(d);
+    const double lij = a[j] * r;
+    if (lane == j) dinv = r;
+    a[j] = lij;
 #pragma unroll
-    for (int i = j + 1; i < NJ; ++i) {
-      const bool fi = (mask >> i) & 1u;
-      double t = (fi && fj) ? A[i][j] : 0.0;
-#pragma unroll
-      for (int k = 0; k < j; ++k) t -= L[i][k] * L[j][k];
-      L[i][j] = t * il;
-    }
+    for (int k = j + 1; k < NJ; ++k) a[k] -= lij * shfl_d(lij, k);
   }
   return ok;
 }
-// x = (L L^T)^-1 b with divisions replaced by the stored reciprocal diagonal
-FFMPC_DEV void chol7_solve(const double L[NJ][NJ], const double Li[NJ][NJ], double *b) {
+
+// Row `lane` (= column, symmetric) of (L L^T)^-1 restricted to the free set, from the factor stored in shared
+// memory: LL[i*8+j] = L[i][j] (j <= i), DI[i] = 1 / L[i][i].  Clamped rows / columns come out as zero.
+FFMPC_DEV void dist_inverse_row(const double *LL, const double *DI, unsigned mask, int lane, double *x) {
+  const int c = lane < NJ ? lane : NJ - 1;
 #pragma unroll
   for (int i = 0; i < NJ; ++i) {
-    double s = b[i];
+    double s = (i == c) ? 1.0 : 0.0;
 #pragma unroll
-    for (int k = 0; k < i; ++k) s -= L[i][k] * b[k];
-    b[i] = s * Li[i][i];
+    for (int k = 0; k < i; ++k) s -= LL[i * 8 + k] * x[k];
+    x[i] = s * DI[i];
   }
 #pragma unroll
   for (int i = NJ - 1; i >= 0; --i) {
-    double s = b[i];
+    double s = x[i];
 #pragma unroll
-    for (int k = i + 1; k < NJ; ++k) s -= L[k][i] * b[k];
-    b[i] = s * Li[i][i];
+    for (int k = i + 1; k < NJ; ++k) s -= LL[k * 8 + i] * x[k];
+    x[i] = s * DI[i];
   }
+  const bool fc = (mask >> c) & 1u;
+#pragma unroll
+  for (int i = 0; i < NJ; ++i)
+    if (!(fc && ((mask >> i) & 1u))) x[i] = 0.0;
 }
-// masked inverse: Hinv = (H_ff)^-1 embedded in 7x7, zero on clamped rows/cols
-FFMPC_DEV bool masked_inverse7(const double H[NJ][NJ], unsigned mask, double reg, double Hinv[NJ][NJ]) {
-  double A[NJ][NJ], L[NJ][NJ], Li[NJ][NJ];
+
+// factor + inverse: hrow = row `lane` of H (+ reg on the diagonal), hi = row `lane` of the masked inverse.
+// LL / DI are 64 + 8 doubles of warp-private shared memory.
+FFMPC_DEV bool dist_masked_inverse(const double *hrow, unsigned mask, double reg, int lane, double *LL, double *DI, double *hi) {
+  double a[NJ], dinv;
 #pragma unroll
-  for (int i = 0; i < NJ; ++i)
+  for (int j = 0; j < NJ; ++j) a[j] = hrow[j] + ((lane == j) ? reg : 0.0);
+  const bool ok = dist_chol7(a, mask, lane, dinv);
+  __syncwarp();
+  if (lane < NJ) {
 #pragma unroll
-    for (int j = 0; j < NJ; ++j) A[i][j] = H[i][j] + ((i == j) ? reg : 0.0);
-  if (!chol7(A, mask, L, Li)) return false;
-#pragma unroll
-  for (int j = 0; j < NJ; ++j)
-#pragma unroll
-    for (int i = j + 1; i < NJ; ++i) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = j; k < i; ++k) s -= L[i][k] * Li[k][j];
-      Li[i][j] = s * Li[i][i];
-    }
-#pragma unroll
-  for (int i = 0; i < NJ; ++i)
-#pragma unroll
-    for (int j = 0; j <= i; ++j) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = i; k < NJ; ++k) s += Li[k][i] * Li[k][j];
-      const bool f = ((mask >> i) & 1u) && ((mask >> j) & 1u);
-      Hinv[i][j] = f ? s : 0.0;
-      Hinv[j][i] = Hinv[i][j];
-    }
+    for (int j = 0; j < NJ; ++j) LL[lane * 8 + j] = a[j];
+    DI[lane] = dinv;
+  }
+  __syncwarp();
+  if (!ok) return false;
+  dist_inverse_row(LL, DI, mask, lane, hi);
   return true;
 }
 
-// crocoddyl::BoxQP::solve (projected Newton, Tassa 2014), SURVEY App. A.8.
-//   x: in = warm start, out = solution;  mask out = free set;  Hinv = free-block inverse (masked)
-FFMPC_DEV bool boxqp7(const ffmpc_config &cfg, const double H[NJ][NJ], const double *q, const double *lb, const double *ub,
-                      double *x, unsigned &mask_out, double Hinv[NJ][NJ]) {
-#pragma unroll
-  for (int i = 0; i < NJ; ++i) x[i] = fmax(fmin(x[i], ub[i]), lb[i]);
+// crocoddyl::BoxQP::solve (projected Newton, Tassa 2014), SURVEY App. A.8, rows distributed over lanes 0..6.
+//   hrow: row of H; q, lb, ub, x: component `lane`;  x: in = warm start, out = solution;
+//   mask_out = free set;  hi = row `lane` of the free-block inverse (zero on clamped rows / columns)
+FFMPC_DEV bool dist_boxqp7(const ffmpc_config &cfg, const double *hrow, double q, double lb, double ub, double &x, int lane,
+                           double *LL, double *DI, unsigned &mask_out, double *hi) {
+  const bool act = lane < NJ;
+  x = fmax(fmin(x, ub), lb);
   unsigned inv_mask = 0xffffffffu, mask = 0;
   bool ok = true;
   for (int it = 0; it < cfg.boxqp_maxiter; ++it) {
-    double g[NJ], gnorm = 0.0;
-    mask = 0;
+    double xv[NJ];
+    gather7(x, xv);
+    double hx = 0.0;
 #pragma unroll
-    for (int i = 0; i < NJ; ++i) {
-      double gi = q[i];
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) gi += H[i][j] * x[j];
-      g[i] = gi;
-      gnorm = fmax(gnorm, fabs(gi));
-      const bool clamped = (x[i] == lb[i] && gi > 0.0) || (x[i] == ub[i] && gi < 0.0);
-      if (!clamped) mask |= 1u << i;
-    }
+    for (int j = 0; j < NJ; ++j) hx += hrow[j] * xv[j];
+    const double g = q + hx;
+    const bool clamped = (x == lb && g > 0.0) || (x == ub && g < 0.0);
+    mask = __ballot_sync(0xffffffffu, act && !clamped) & 0x7fu;
+    const double gnorm = max8(act ? fabs(g) : 0.0);
     if (gnorm <= cfg.boxqp_th_grad || mask == 0) {
       if (it == 0 || mask != inv_mask) {
-        if (!masked_inverse7(H, mask, cfg.boxqp_reg, Hinv)) ok = false;
+        if (!dist_masked_inverse(hrow, mask, cfg.boxqp_reg, lane, LL, DI, hi)) ok = false;
         inv_mask = mask;
       }
       break;
     }
-    if (!masked_inverse7(H, mask, cfg.boxqp_reg, Hinv)) { ok = false; break; }
+    if (!dist_masked_inverse(hrow, mask, cfg.boxqp_reg, lane, LL, DI, hi)) { ok = false; break; }
     inv_mask = mask;
-    double r[NJ], dx[NJ];
+    const bool fr = (mask >> (act ? lane : 0)) & 1u;
+    // r = -q - H[:, clamped] x_clamped on the free rows
+    double s = -q;
 #pragma unroll
-    for (int i = 0; i < NJ; ++i) {
-      double s = -q[i];
+    for (int j = 0; j < NJ; ++j)
+      if (!((mask >> j) & 1u)) s -= hrow[j] * xv[j];
+    double rv[NJ];
+    gather7((act && fr) ? s : 0.0, rv);
+    double hr = 0.0;
 #pragma unroll
-      for (int j = 0; j < NJ; ++j)
-        if (!((mask >> j) & 1u)) s -= H[i][j] * x[j];
-      r[i] = ((mask >> i) & 1u) ? s : 0.0;
-    }
-#pragma unroll
-    for (int i = 0; i < NJ; ++i) {
-      double s = 0.0;
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) s += Hinv[i][j] * r[j];
-      dx[i] = ((mask >> i) & 1u) ? s - x[i] : 0.0;
-    }
-    double fold = 0.0;
-#pragma unroll
-    for (int i = 0; i < NJ; ++i) {
-      double hy = 0.0;
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) hy += H[i][j] * x[j];
-      fold += 0.5 * x[i] * hy + q[i] * x[i];
-    }
+    for (int j = 0; j < NJ; ++j) hr += hi[j] * rv[j];
+    const double dx = (act && fr) ? hr - x : 0.0;
+    const double fold = sum8(act ? (0.5 * x * hx + q * x) : 0.0);
     bool changed = false;
     double steplength = 1.0;
     for (int ia = 0; ia < cfg.n_alphas; ++ia, steplength *= 0.5) {
-      double xn[NJ], fnew = 0.0, gd = 0.0;
+      const double xn = fmax(fmin(x + steplength * dx, ub), lb);
+      double xnv[NJ];
+      gather7(xn, xnv);
+      double hy = 0.0;
 #pragma unroll
-      for (int i = 0; i < NJ; ++i) xn[i] = fmax(fmin(x[i] + steplength * dx[i], ub[i]), lb[i]);
-#pragma unroll
-      for (int i = 0; i < NJ; ++i) {
-        double hy = 0.0;
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) hy += H[i][j] * xn[j];
-        fnew += 0.5 * xn[i] * hy + q[i] * xn[i];
-        gd += g[i] * (x[i] - xn[i]);
-      }
+      for (int j = 0; j < NJ; ++j) hy += hrow[j] * xnv[j];
+      const double fnew = sum8(act ? (0.5 * xn * hy + q * xn) : 0.0);
+      const double gd = sum8(act ? g * (x - xn) : 0.0);
       if (fold - fnew > cfg.boxqp_th_acceptstep * gd) {
-#pragma unroll
-        for (int i = 0; i < NJ; ++i) {
-          if (xn[i] != x[i]) changed = true;
-          x[i] = xn[i];
-        }
+        changed = __any_sync(0xffffffffu, act && xn != x) != 0;
+        x = xn;
         break;
       }
     }
-    // iteration map is a deterministic function of x: nothing changes any more (see oracle)
+    // the iteration map is a deterministic function of x: nothing changes any more (see oracle)
     if (!changed) break;
   }
   mask_out = mask;
   return ok;
 }
 
-FFMPC_DEV double warp_sum(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
 // ------------------------------------------------------------------------------------------------
 // k_backward: Riccati sweep, one warp per instance, lane c owns column c of the nx-wide matrices.
 // With Fx = Pt + Et Gh (Pt: Euler/LPF structure, Et = [dt I; I; 0], Gh = dt * d a/dz) the products
 // Fx^T V Fx etc. are evaluated in the factored form of DESIGN.md section "Backward kernel".
+// The 7x7 gain algebra (LLT / BoxQP) is row-distributed over lanes 0..6 (dist_* above).
 // ------------------------------------------------------------------------------------------------
 template <bool FF> struct BwdLayout {
   static constexpr int n = FF ? 21 : 14;
-  static constexpr int LD = FF ? 21 : 15;  // odd leading dimension: conflict-free column reads
+  static constexpr int LD = FF ? 21 : 15;  // odd leading dimension: conflict-free column AND row reads
   static constexpr int oREC = 0;
   static constexpr int oV = oREC + REC_SIZE;
   static constexpr int oVE = oV + n * LD + (n * LD) % 2;
@@ -403,11 +404,12 @@ template <bool FF> struct BwdLayout {
   static constexpr int oGT = oYS + n * 8;
   static constexpr int oQXU = oGT + n * 8;
   static constexpr int oSS = oQXU + n * 8;
-  static constexpr int oQUU = oSS + 56;
-  static constexpr int oVX = oQUU + 56;
+  static constexpr int oLL = oSS + 56;   // Cholesky factor rows
+  static constexpr int oHI = oLL + 56;   // (masked) inverse of Quu, rows
+  static constexpr int oVX = oHI + 56;
   static constexpr int oFS = oVX + 24;
-  static constexpr int oQU = oFS + 24;
-  static constexpr int TOTAL = oQU + 8;  // doubles per warp
+  static constexpr int oDI = oFS + 24;   // reciprocal pivots
+  static constexpr int TOTAL = oDI + 8;  // doubles per warp
 };
 
 template <bool FF>
@@ -419,13 +421,14 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
   const int N = ws.N;
   const int lane = (int)(threadIdx.x & 31);
   const int c = lane < n ? lane : n - 1;  // inactive lanes shadow the last column (no writes)
-  const bool act = lane < n;
+  const int r7 = lane < NJ ? lane : NJ - 1;
+  const bool act = lane < n, act7 = lane < NJ;
   const double dt = cfg.dt_ocp;
   const double alpha = fmin(fmax(cfg.ff_alpha, 0.0), 0.999999), beta = 1.0 - alpha;
   const bool box = cfg.use_box_fddp && feasible;
   double *REC = sm + LYT::oREC, *V = sm + LYT::oV, *VEs = sm + LYT::oVE, *YS = sm + LYT::oYS, *GT = sm + LYT::oGT,
-         *QXU = sm + LYT::oQXU, *SS = sm + LYT::oSS, *QUU = sm + LYT::oQUU, *VX = sm + LYT::oVX, *FS = sm + LYT::oFS,
-         *QU = sm + LYT::oQU;
+         *QXU = sm + LYT::oQXU, *SS = sm + LYT::oSS, *LL = sm + LYT::oLL, *HI = sm + LYT::oHI, *VX = sm + LYT::oVX,
+         *FS = sm + LYT::oFS, *DI = sm + LYT::oDI;
   const double *recb = ws.rec + (size_t)b * (N + 1) * REC_SIZE;
   const double *fsb = ws.fs + (size_t)b * (N + 1) * n;
   const double *usb = ws.us + ((size_t)ws.cur[b] * ws.B + b) * N * NJ;
@@ -433,22 +436,23 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
   double *kb = ws.k + (size_t)b * N * NJ;
   double *Vfsb = ws.Vfs + (size_t)b * (N + 1) * n;
   double dg = 0.0, dq = 0.0;
+  // packed-upper index of Lzz(i, c): i <= c -> base_i + c (base_i compile-time), i > c -> colbase + i
+  const int colbase = c * NZ - (c * (c - 1)) / 2 - c;
+#define LZZ_AT(i) REC[REC_LZZ + (((i) <= c) ? ((i) * NZ - ((i) * ((i) - 1)) / 2 - (i) + c) : (colbase + (i)))]
 
   // ---- terminal knot: Vxx = Lxx + preg, Vx = Lx (+ Vxx fs) ----
   for (int i = lane; i < REC_SIZE; i += 32) REC[i] = recb[(size_t)N * REC_SIZE + i];
   if (act) FS[lane] = fsb[N * n + lane];
   __syncwarp();
   {
-    double vcol[n];
-#pragma unroll
-    for (int i = 0; i < n; ++i) {
-      vcol[i] = REC[REC_LZZ + sym_idx_any(i, c)] + ((i == c) ? preg : 0.0);
-      if (act) V[i * LD + c] = vcol[i];
-    }
-    double vx = REC[REC_LZ + c];
     double vf = 0.0;
 #pragma unroll
-    for (int i = 0; i < n; ++i) vf += vcol[i] * FS[i];
+    for (int i = 0; i < n; ++i) {
+      const double vi = LZZ_AT(i) + ((i == c) ? preg : 0.0);
+      if (act) V[i * LD + c] = vi;
+      vf += vi * FS[i];
+    }
+    double vx = REC[REC_LZ + c];
     if (!feasible) vx += vf;
     if (act) {
       VX[lane] = vx;
@@ -466,16 +470,16 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     if (act) FS[lane] = fsb[t * n + lane];
     __syncwarp();
     const double *G = REC + REC_G;
-    // Gh[:,c] = dt * G[:,c]
-    double g[NJ];
-#pragma unroll
-    for (int k = 0; k < NJ; ++k) g[k] = dt * G[k * NZ + c];
-    // (b) VE = V Et : row c
-    double ve[NJ];
+    // (a) Gh[:,c] = dt * G[:,c] ; (b) VE = V Et : row c
+    double g[NJ], ve[NJ];
 #pragma unroll
     for (int k = 0; k < NJ; ++k) {
+      g[k] = dt * G[k * NZ + c];
       ve[k] = dt * V[k * LD + c] + V[(NJ + k) * LD + c];
-      if (act) VEs[c * 8 + k] = ve[k];
+      if (act) {
+        VEs[c * 8 + k] = ve[k];
+        GT[c * 8 + k] = g[k];
+      }
     }
     __syncwarp();
     // (c) S = Et^T V Et
@@ -485,39 +489,46 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     }
     __syncwarp();
     // (d) Tt = Pt^T V Et (row c), Y = Tt + Gh^T S (row c)
-    double tt[NJ], y[NJ];
+    double tt[NJ];
 #pragma unroll
     for (int k = 0; k < NJ; ++k) {
       if (c < NJ) tt[k] = ve[k];
       else if (c < 2 * NJ) tt[k] = SS[(c - NJ) * 8 + k];
       else tt[k] = alpha * ve[k];
     }
+    {
+      double y[NJ];
 #pragma unroll
-    for (int l = 0; l < NJ; ++l) {
-      double s = tt[l];
+      for (int l = 0; l < NJ; ++l) y[l] = tt[l];
 #pragma unroll
-      for (int k = 0; k < NJ; ++k) s += g[k] * SS[k * 8 + l];
-      y[l] = s;
-    }
-    if (act) {
+      for (int k = 0; k < NJ; ++k)
 #pragma unroll
-      for (int k = 0; k < NJ; ++k) {
-        YS[c * 8 + k] = y[k];
-        GT[c * 8 + k] = g[k];
+        for (int l = 0; l < NJ; ++l) y[l] += g[k] * SS[k * 8 + l];
+      if (act) {
+#pragma unroll
+        for (int k = 0; k < NJ; ++k) YS[c * 8 + k] = y[k];
+      }
+      // (g) Qxu row c (classical: Lxu + Y Gu)
+      if (!FF) {
+#pragma unroll
+        for (int a = 0; a < NJ; ++a) {
+          double s = REC[REC_LZZ + sym_idx(c, 2 * NJ + a)];
+#pragma unroll
+          for (int k = 0; k < NJ; ++k) s += y[k] * (dt * G[k * NZ + 2 * NJ + a]);
+          if (act) QXU[c * 8 + a] = s;
+        }
       }
     }
     // (f) Qx
-    double e7[NJ];
-#pragma unroll
-    for (int k = 0; k < NJ; ++k) e7[k] = dt * VX[k] + VX[NJ + k];
     double qx = REC[REC_LZ + c];
-    if (c < NJ) qx += VX[c];
-    else if (c < 2 * NJ) qx += VX[c] + dt * VX[c - NJ];
-    else qx += alpha * VX[c];
+    {
+      if (c < NJ) qx += VX[c];
+      else if (c < 2 * NJ) qx += VX[c] + dt * VX[c - NJ];
+      else qx += alpha * VX[c];
 #pragma unroll
-    for (int k = 0; k < NJ; ++k) qx += g[k] * e7[k];
-    // (g) Qxu row c
-    double qxu[NJ];
+      for (int k = 0; k < NJ; ++k) qx += g[k] * (dt * VX[k] + VX[NJ + k]);
+    }
+    // (g) Qxu row c (FF: beta * (Fx^T V)[:, tau])
     if (FF) {
 #pragma unroll
       for (int a = 0; a < NJ; ++a) {
@@ -526,130 +537,131 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
         if (c >= 2 * NJ) pc *= alpha;
 #pragma unroll
         for (int k = 0; k < NJ; ++k) pc += g[k] * VEs[(2 * NJ + a) * 8 + k];
-        qxu[a] = beta * pc;
+        if (act) QXU[c * 8 + a] = beta * pc;
       }
+    }
+    // (h) Quu row r7 (+ preg on the diagonal), Qu[r7]  -- lanes 0..6, the others shadow row 6
+    double qrow[NJ], qu;
+    if (FF) {
+#pragma unroll
+      for (int bb = 0; bb < NJ; ++bb)
+        qrow[bb] = ((r7 == bb) ? REC[REC_LWW + r7] + preg : 0.0) + beta * beta * V[(2 * NJ + r7) * LD + 2 * NJ + bb];
+      qu = REC[REC_LW + r7] + beta * VX[2 * NJ + r7];
     } else {
+      double sb[NJ];
 #pragma unroll
-      for (int a = 0; a < NJ; ++a) {
-        double s = REC[REC_LZZ + sym_idx(c, 2 * NJ + a)];
-#pragma unroll
-        for (int k = 0; k < NJ; ++k) s += y[k] * (dt * G[k * NZ + 2 * NJ + a]);
-        qxu[a] = s;
-      }
-    }
-    if (act) {
-#pragma unroll
-      for (int a = 0; a < NJ; ++a) QXU[c * 8 + a] = qxu[a];
-    }
-    // (h) Quu column `lane`, Qu[lane] for lane < 7
-    if (lane < NJ) {
-      const int a = lane;
-      if (FF) {
-#pragma unroll
-        for (int bb = 0; bb < NJ; ++bb)
-          QUU[bb * 8 + a] = ((a == bb) ? REC[REC_LWW + a] : 0.0) + beta * beta * V[(2 * NJ + bb) * LD + 2 * NJ + a];
-        QU[a] = REC[REC_LW + a] + beta * VX[2 * NJ + a];
-      } else {
-        double sb[NJ];
-#pragma unroll
-        for (int k = 0; k < NJ; ++k) {
-          double s = 0.0;
-#pragma unroll
-          for (int m = 0; m < NJ; ++m) s += SS[k * 8 + m] * (dt * G[m * NZ + 2 * NJ + a]);
-          sb[k] = s;
-        }
-        double qu = REC[REC_LZ + 2 * NJ + a];
-#pragma unroll
-        for (int bb = 0; bb < NJ; ++bb) {
-          double s = REC[REC_LZZ + sym_idx_any(2 * NJ + bb, 2 * NJ + a)];
-#pragma unroll
-          for (int k = 0; k < NJ; ++k) s += (dt * G[k * NZ + 2 * NJ + bb]) * sb[k];
-          QUU[bb * 8 + a] = s;
-        }
-#pragma unroll
-        for (int k = 0; k < NJ; ++k) qu += (dt * G[k * NZ + 2 * NJ + a]) * e7[k];
-        QU[a] = qu;
-      }
-    }
-    __syncwarp();
-    // (e) Qxx column c
-    double qxx[n];
-    {
-      double w[n];
-#pragma unroll
-      for (int i = 0; i < n; ++i) {
-        double wi = V[i * LD + c];
-        if (c >= NJ && c < 2 * NJ) wi += dt * V[i * LD + c - NJ];
-        if (FF && c >= 2 * NJ) wi *= alpha;
-        w[i] = wi;
-      }
-#pragma unroll
-      for (int i = 0; i < n; ++i) {
-        double acc = w[i];
-        if (i >= NJ && i < 2 * NJ) acc += dt * w[i - NJ];
-        if (FF && i >= 2 * NJ) acc *= alpha;
-        acc += REC[REC_LZZ + sym_idx_any(i, c)];
-#pragma unroll
-        for (int k = 0; k < NJ; ++k) acc += YS[i * 8 + k] * g[k] + GT[i * 8 + k] * tt[k];
-        qxx[i] = acc;
-      }
-    }
-    // (i) gains -- every lane runs the 7x7 algebra redundantly (uniform data)
-    double Q[NJ][NJ], qu[NJ], kv[NJ], kc[NJ];
-#pragma unroll
-    for (int i = 0; i < NJ; ++i) {
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) Q[i][j] = QUU[i * 8 + j] + ((i == j) ? preg : 0.0);
-      qu[i] = QU[i];
-    }
-    if (!box) {
-      double L[NJ][NJ], Li[NJ][NJ];
-      if (!chol7(Q, 0x7fu, L, Li)) return false;
-#pragma unroll
-      for (int a = 0; a < NJ; ++a) { kc[a] = qxu[a]; kv[a] = qu[a]; }
-      chol7_solve(L, Li, kc);
-      chol7_solve(L, Li, kv);
-    } else {
-      double lb[NJ], ub[NJ], xq[NJ], Hinv[NJ][NJ];
-#pragma unroll
-      for (int a = 0; a < NJ; ++a) {
-        const double u0 = usb[t * NJ + a];
-        lb[a] = -cfg.tau_limits[a] - u0;
-        ub[a] = cfg.tau_limits[a] - u0;
-        xq[a] = kb[t * NJ + a];  // warm start = stored k_t (crocoddyl passes k_[t])
-      }
-      unsigned mask;
-      if (!boxqp7(cfg, Q, qu, lb, ub, xq, mask, Hinv)) return false;
-#pragma unroll
-      for (int a = 0; a < NJ; ++a) {
+      for (int k = 0; k < NJ; ++k) {
         double s = 0.0;
 #pragma unroll
-        for (int bb = 0; bb < NJ; ++bb) s += Hinv[a][bb] * qxu[bb];
-        kc[a] = s;
-        kv[a] = -xq[a];
-        if (!((mask >> a) & 1u)) qu[a] = 0.0;  // clamped directions do not count for the stopping measure
+        for (int m = 0; m < NJ; ++m) s += SS[k * 8 + m] * (dt * G[m * NZ + 2 * NJ + r7]);
+        sb[k] = s;
       }
+      qu = REC[REC_LZ + 2 * NJ + r7];
+#pragma unroll
+      for (int bb = 0; bb < NJ; ++bb) {
+        double s = REC[REC_LZZ + sym_idx_any(2 * NJ + bb, 2 * NJ + r7)] + ((r7 == bb) ? preg : 0.0);
+#pragma unroll
+        for (int k = 0; k < NJ; ++k) s += (dt * G[k * NZ + 2 * NJ + bb]) * sb[k];
+        qrow[bb] = s;
+      }
+#pragma unroll
+      for (int k = 0; k < NJ; ++k) qu += (dt * G[k * NZ + 2 * NJ + r7]) * (dt * VX[k] + VX[NJ + k]);
     }
-    __syncwarp();  // all lanes have read k_t / QUU / QU before they are overwritten
+    __syncwarp();  // YS / GT / QXU visible to every lane
+    // (e) Qxx column c
+    double qxx[n];
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      double wi = V[i * LD + c];
+      if (c >= NJ && c < 2 * NJ) wi += dt * V[i * LD + c - NJ];
+      if (FF && c >= 2 * NJ) wi *= alpha;
+      qxx[i] = wi;
+    }
+#pragma unroll
+    for (int i = n - 1; i >= 0; --i) {
+      double acc = qxx[i];
+      if (i >= NJ && i < 2 * NJ) acc += dt * qxx[i - NJ];
+      if (FF && i >= 2 * NJ) acc *= alpha;
+      acc += LZZ_AT(i);
+#pragma unroll
+      for (int k = 0; k < NJ; ++k) acc += YS[i * 8 + k] * g[k] + GT[i * 8 + k] * tt[k];
+      qxx[i] = acc;
+    }
+    // (i) gains.  LLT path (crocoddyl computeGains: Quu_llt.solve): factor row-distributed, then lane c solves
+    //     Quu K[:,c] = Qxu[c,:]^T by substitution with the factor broadcast from shared memory; lane n does the same
+    //     for Qu.  BoxQP path: K = (Quu_ff)^-1 Qxu^T with the masked inverse, k = -x*.
+    double kc[NJ], kvv[NJ], kv;
+    if (!box) {
+      double a[NJ], dinv;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) a[j] = qrow[j];
+      const bool okc = dist_chol7(a, 0x7fu, lane, dinv);
+      if (act7) {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) LL[lane * 8 + j] = a[j];
+        DI[lane] = dinv;
+      }
+      __syncwarp();
+      if (!okc) return false;
+      double quv[NJ];
+      gather7(qu, quv);
+#pragma unroll
+      for (int i = 0; i < NJ; ++i) {
+        double s2 = (lane == n) ? quv[i] : QXU[c * 8 + i];
+#pragma unroll
+        for (int k = 0; k < i; ++k) s2 -= LL[i * 8 + k] * kc[k];
+        kc[i] = s2 * DI[i];
+      }
+#pragma unroll
+      for (int i = NJ - 1; i >= 0; --i) {
+        double s2 = kc[i];
+#pragma unroll
+        for (int k = i + 1; k < NJ; ++k) s2 -= LL[k * 8 + i] * kc[k];
+        kc[i] = s2 * DI[i];
+      }
+#pragma unroll
+      for (int i = 0; i < NJ; ++i) kvv[i] = shfl_d(kc[i], n);
+      kv = kvv[0];
+#pragma unroll
+      for (int i = 1; i < NJ; ++i) kv = (r7 == i) ? kvv[i] : kv;
+    } else {
+      double hi[NJ];
+      const double u0 = usb[t * NJ + r7];
+      const double lb = -cfg.tau_limits[r7] - u0, ub = cfg.tau_limits[r7] - u0;
+      double xq = kb[t * NJ + r7];  // warm start = stored k_t (crocoddyl passes k_[t])
+      unsigned mask;
+      if (!dist_boxqp7(cfg, qrow, qu, lb, ub, xq, lane, LL, DI, mask, hi)) return false;
+      kv = -xq;
+      if (!((mask >> r7) & 1u)) qu = 0.0;  // clamped directions do not count for the stopping measure
+      __syncwarp();
+      if (act7) {
+#pragma unroll
+        for (int bb = 0; bb < NJ; ++bb) HI[lane * 8 + bb] = hi[bb];
+      }
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < NJ; ++a) kc[a] = 0.0;
+#pragma unroll
+      for (int bb = 0; bb < NJ; ++bb) {
+        const double qb = QXU[c * 8 + bb];
+#pragma unroll
+        for (int a = 0; a < NJ; ++a) kc[a] += HI[a * 8 + bb] * qb;
+      }
+      gather7(kv, kvv);
+    }
+    if (act7) kb[t * NJ + lane] = kv;
     if (act) {
 #pragma unroll
       for (int a = 0; a < NJ; ++a) Kb[((size_t)t * NJ + a) * n + c] = kc[a];
     }
-    if (lane < NJ) kb[t * NJ + lane] = kv[lane];
-    // value function
+    // value function: wv = Quu k - 2 Qu (row r7), dg += Qu.k, dq -= k.Quu k
     double wv[NJ];
-    double dgt = 0.0, dqt = 0.0;
+    double qk = 0.0;
 #pragma unroll
-    for (int a = 0; a < NJ; ++a) {
-      double s = 0.0;
-#pragma unroll
-      for (int bb = 0; bb < NJ; ++bb) s += Q[a][bb] * kv[bb];
-      wv[a] = s - 2.0 * qu[a];
-      dgt += qu[a] * kv[a];
-      dqt += kv[a] * s;
-    }
-    dg += dgt;
-    dq -= dqt;
+    for (int bb = 0; bb < NJ; ++bb) qk += qrow[bb] * kvv[bb];
+    gather7(qk - 2.0 * qu, wv);
+    dg += sum8(act7 ? qu * kv : 0.0);
+    dq -= sum8(act7 ? kv * qk : 0.0);
     double vx = qx;
 #pragma unroll
     for (int a = 0; a < NJ; ++a) vx += kc[a] * wv[a];
@@ -688,13 +700,14 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     if (__any_sync(0xffffffffu, bad && act)) return false;
     __syncwarp();
   }
+#undef LZZ_AT
   dg_out = dg;
   dq_out = dq;
   return true;
 }
 
 template <bool FF>
-__global__ void __launch_bounds__(128) k_backward(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(128, 4) k_backward(const __grid_constant__ Params P) {
 #ifdef FFMPC_EMU
   double *smem = (double *)emu::S().smem;
 #else
@@ -738,125 +751,195 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ Params
 
 // ------------------------------------------------------------------------------------------------
 // k_forward: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update
+//
+// Parallel line search: instance b is served by A = 2^a adjacent lanes of one warp; lane j rolls out step
+// length alpha = 2^-(r A + j) in round r into its OWN trial buffer, then the group elects the FIRST (largest)
+// accepted alpha -- the same decision the sequential loop of SolverFDDP::solve takes, because a trial never
+// depends on another trial.  xs / us live in (A_max + 1) trajectory slots per instance; `cur[b]` names the
+// accepted one and lane j writes slot j + (j >= cur).
 // ------------------------------------------------------------------------------------------------
 template <int NC, bool FF>
-__global__ void __launch_bounds__(128) k_forward(const __grid_constant__ Params P, int it) {
+FFMPC_DEV bool rollout(const Params &P, int b, int cur, int slot, double steplength, bool feasible, double &cost_try, double &dv_out,
+                       double *lam01) {
   const Workspace &ws = P.ws;
   const ffmpc_config &cfg = P.cfg;
   constexpr int nx = FF ? 21 : 14;
   const int N = ws.N;
-  const int slot = global_tid();
-  const int nfree = ws.counts[0];
-  const int cnt = (NC == 0) ? nfree : ws.counts[1];
-  if (slot >= cnt) return;
-  const int b = ws.perm[(NC == 0 ? 0 : nfree) + slot];
-  if (ws.done[b]) return;
-  const int cur = ws.cur[b];
   const double *xs = ws.xs + ((size_t)cur * ws.B + b) * (N + 1) * nx;
   const double *us = ws.us + ((size_t)cur * ws.B + b) * N * NJ;
-  double *xt_all = ws.xs + ((size_t)(1 - cur) * ws.B + b) * (N + 1) * nx;
-  double *ut_all = ws.us + ((size_t)(1 - cur) * ws.B + b) * N * NJ;
+  double *xt_all = ws.xs + ((size_t)slot * ws.B + b) * (N + 1) * nx;
+  double *ut_all = ws.us + ((size_t)slot * ws.B + b) * N * NJ;
   const double *fs = ws.fs + (size_t)b * (N + 1) * nx;
   const double *Vfs = ws.Vfs + (size_t)b * (N + 1) * nx;
   const double *Kb = ws.K + (size_t)b * N * NJ * nx;
   const double *kb = ws.k + (size_t)b * N * NJ;
   const double *x0 = ws.x0 + (size_t)b * nx;
-  const bool feasible = ws.feas[b] != 0;
-  double cost = ws.cost[b];
-  if (!ws.cost_valid[b]) {
-    // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
-    cost = 0.0;
-    for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
-    ws.cost_valid[b] = 1;
-  }
-  const double dg = ws.dg[b], dq = ws.dq[b];
   KnotCtx ctx;
   ctx.x_reg_ref = ws.x_reg_ref + (size_t)b * 14;
   ctx.tau_ref = ws.tau_ref + (size_t)b * NJ;
   ctx.y_ref = x0;
-
-  double steplength = 1.0, d1 = ws.d1[b], d2 = ws.d2[b], cost_try = 0.0;
-  bool accepted = false;
-  for (int ia = 0; ia < cfg.n_alphas; ++ia) {
-    steplength = ldexp(1.0, -ia);
-    const bool close = feasible || (steplength == 1.0);
-    double xh[nx];
+  const bool close = feasible || (steplength == 1.0);
+  double xh[nx];
 #pragma unroll
-    for (int i = 0; i < nx; ++i) xh[i] = x0[i];
-    cost_try = 0.0;
-    double dv = 0.0;
-    bool okr = true;
-    for (int t = 0; t <= N; ++t) {
-      double xt[nx], dx[nx];
-      double dvt = 0.0;
+  for (int i = 0; i < nx; ++i) xh[i] = x0[i];
+  cost_try = 0.0;
+  double dv = 0.0;
+  for (int t = 0; t <= N; ++t) {
+    double xt[nx], dx[nx];
+    double dvt = 0.0;
 #pragma unroll
-      for (int i = 0; i < nx; ++i) {
-        xt[i] = close ? xh[i] : xh[i] + fs[t * nx + i] * (steplength - 1.0);
-        xt_all[t * nx + i] = xt[i];
-        dx[i] = xt[i] - xs[t * nx + i];
-        dvt += Vfs[t * nx + i] * dx[i];  // = -fs_t^T Vxx_t (xs_t - xs_try_t)
-      }
-      if (!feasible) dv += dvt;
-      double u[NJ];
-      if (t < N) {
-#pragma unroll
-        for (int a = 0; a < NJ; ++a) {
-          double s = us[t * NJ + a] - kb[t * NJ + a] * steplength;
-          double kd = 0.0;
-          const double *Krow = Kb + ((size_t)t * NJ + a) * nx;
-#pragma unroll
-          for (int j = 0; j < nx; ++j) kd += Krow[j] * dx[j];
-          s -= kd;
-          if (cfg.use_box_fddp) s = fmin(fmax(s, -cfg.tau_limits[a]), cfg.tau_limits[a]);
-          u[a] = s;
-          ut_all[t * NJ + a] = s;
-        }
-      } else {
-#pragma unroll
-        for (int a = 0; a < NJ; ++a) u[a] = 0.0;
-      }
-      ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
-      ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
-      ctx.terminal = (t == N);
-      double cst, lam[3];
-      action_node<NC, FF, false>(P.mdl, cfg, ctx, xt, u, xh, &cst, lam, nullptr);
-      if (NC != 0 && t < 2) {
-        ws.f_pred[b * 6 + t * 3 + 0] = lam[0];
-        ws.f_pred[b * 6 + t * 3 + 1] = lam[1];
-        ws.f_pred[b * 6 + t * 3 + 2] = lam[2];
-      }
-      cost_try += cst;
-      bool fin = isfinite(cost_try);
-      if (t < N) {
-#pragma unroll
-        for (int i = 0; i < nx; ++i) fin = fin && isfinite(xh[i]);
-      }
-      if (!fin) { okr = false; break; }
+    for (int i = 0; i < nx; ++i) {
+      xt[i] = close ? xh[i] : xh[i] + fs[t * nx + i] * (steplength - 1.0);
+      xt_all[t * nx + i] = xt[i];
+      dx[i] = xt[i] - xs[t * nx + i];
+      dvt += Vfs[t * nx + i] * dx[i];  // = -fs_t^T Vxx_t (xs_t - xs_try_t)
     }
-    if (!okr) continue;  // "forward_error": try the next step length
-    const double dV = cost - cost_try;
-    d1 = dg + dv;
-    d2 = dq - 2.0 * dv;
-    const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
-    if (dVexp >= 0.0) {
-      if (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp) accepted = true;
+    if (!feasible) dv += dvt;
+    double u[NJ];
+    if (t < N) {
+#pragma unroll
+      for (int a = 0; a < NJ; ++a) {
+        double s = us[t * NJ + a] - kb[t * NJ + a] * steplength;
+        double kd = 0.0;
+        const double *Krow = Kb + ((size_t)t * NJ + a) * nx;
+#pragma unroll
+        for (int j = 0; j < nx; ++j) kd += Krow[j] * dx[j];
+        s -= kd;
+        if (cfg.use_box_fddp) s = fmin(fmax(s, -cfg.tau_limits[a]), cfg.tau_limits[a]);
+        u[a] = s;
+        ut_all[t * NJ + a] = s;
+      }
     } else {
-      if (!feasible && dV > cfg.th_acceptnegstep * dVexp) accepted = true;
+#pragma unroll
+      for (int a = 0; a < NJ; ++a) u[a] = 0.0;
     }
-    if (accepted) break;
+    ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
+    ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
+    ctx.terminal = (t == N);
+    double cst, lam[3];
+    action_node<NC, FF, false>(P.mdl, cfg, ctx, xt, u, xh, &cst, lam, nullptr);
+    if (NC != 0 && t < 2) {
+      lam01[t * 3 + 0] = lam[0];
+      lam01[t * 3 + 1] = lam[1];
+      lam01[t * 3 + 2] = lam[2];
+    }
+    cost_try += cst;
+    bool fin = isfinite(cost_try);
+    if (t < N) {
+#pragma unroll
+      for (int i = 0; i < nx; ++i) fin = fin && isfinite(xh[i]);
+    }
+    if (!fin) return false;  // "forward_error": this step length is skipped
   }
+  dv_out = dv;
+  return true;
+}
+
+template <int NC, bool FF>
+__global__ void __launch_bounds__(128) k_forward(const __grid_constant__ Params P, int it, int lgA) {
+  const Workspace &ws = P.ws;
+  const ffmpc_config &cfg = P.cfg;
+  const int N = ws.N;
+  const int A = 1 << lgA;
+  const int g = global_tid();
+  const int lane = (int)(threadIdx.x & 31);
+  const int slot_id = g >> lgA, j = g & (A - 1);
+  const int gbase = lane & ~(A - 1);
+  const unsigned gmask = (A == 32) ? 0xffffffffu : (((1u << A) - 1u) << gbase);
+  const int nfree = ws.counts[0];
+  const int cnt = (NC == 0) ? nfree : ws.counts[1];
+  bool valid = slot_id < cnt;
+  const int b = valid ? ws.perm[(NC == 0 ? 0 : nfree) + slot_id] : 0;
+  if (valid && ws.done[b]) valid = false;
+  if (!__any_sync(0xffffffffu, valid)) return;
+  const int cur = valid ? ws.cur[b] : 0;
+  const bool feasible = valid ? (ws.feas[b] != 0) : false;
+  double cost = 0.0, dg = 0.0, dq = 0.0;
+  if (valid) {
+    cost = ws.cost[b];
+    if (!ws.cost_valid[b]) {
+      // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
+      cost = 0.0;
+      for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
+    }
+    dg = ws.dg[b];
+    dq = ws.dq[b];
+  }
+  const int myslot = j + (j >= cur ? 1 : 0);
+  double d1 = 0.0, d2 = 0.0, cost_try = 0.0;   // of this lane's latest successful rollout
+  double lam01[6] = {NAN, NAN, NAN, NAN, NAN, NAN};
+  int ia_ok = -1;                               // step index of this lane's latest successful rollout
+  int ia_acc = -1;                              // accepted step index of the group
+  int win = -1;                                 // lane (within the warp) that holds the accepted trial
+  const int rounds = (cfg.n_alphas + A - 1) >> lgA;
+  for (int r = 0; r < rounds; ++r) {
+    const int ia = (r << lgA) + j;
+    const bool has = valid && ia_acc < 0 && ia < cfg.n_alphas;
+    bool acc = false;
+    if (has) {
+      const double steplength = ldexp(1.0, -ia);
+      double ct, dv;
+      if (rollout<NC, FF>(P, b, cur, myslot, steplength, feasible, ct, dv, lam01)) {
+        cost_try = ct;
+        ia_ok = ia;
+        const double dV = cost - ct;
+        d1 = dg + dv;
+        d2 = dq - 2.0 * dv;
+        const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
+        if (dVexp >= 0.0) acc = (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp);
+        else acc = (!feasible && dV > cfg.th_acceptnegstep * dVexp);
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, acc) & gmask;
+    if (bal != 0u && ia_acc < 0) {
+      win = __ffs((int)bal) - 1;
+      ia_acc = (r << lgA) + (win - gbase);
+    }
+    if (!__any_sync(0xffffffffu, valid && ia_acc < 0)) break;
+  }
+  // the lane that speaks for the instance: the accepted trial, else the LAST successful trial (d1, d2 keep the
+  // values of the last forwardPass that did not throw), else lane 0 of the group with the stored d1, d2
+  int best = ia_ok;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int other = __shfl_xor_sync(0xffffffffu, best, o);
+    if (o < A && other > best) best = other;
+  }
+  if (!valid) return;
+  const bool accepted = ia_acc >= 0;
+  bool writer;
+  if (accepted) writer = (lane == win);
+  else if (best >= 0) writer = (ia_ok == best);
+  else writer = (j == 0);
+  // contact forces left by the last rollout that ran: the accepted one, else step n_alphas - 1
+  if (NC != 0) {
+    const int ia_last = accepted ? ia_acc : cfg.n_alphas - 1;
+    const bool mine = accepted ? (lane == win) : (ia_last - ((ia_last >> lgA) << lgA) == j);
+    if (mine) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+        if (!isnan(lam01[i]) || accepted) ws.f_pred[b * 6 + i] = lam01[i];
+    }
+  }
+  if (!writer) return;
+  if (!accepted && best < 0) {
+    d1 = ws.d1[b];
+    d2 = ws.d2[b];
+  }
+  const double steplength = accepted ? ldexp(1.0, -ia_acc) : ldexp(1.0, -(cfg.n_alphas - 1));
   double preg = ws.preg[b];
   int wasfeas = ws.wasfeas[b];
   if (accepted) {
     wasfeas = feasible ? 1 : 0;
     ws.wasfeas[b] = wasfeas;
     ws.feas[b] = (wasfeas || steplength == 1.0) ? 1 : 0;
-    ws.cur[b] = 1 - cur;
+    ws.cur[b] = myslot;
     cost = cost_try;
     ws.recalc[b] = 1;
   } else {
     ws.recalc[b] = 0;
   }
+  ws.cost_valid[b] = 1;
   ws.cost[b] = cost;
   ws.d1[b] = d1;
   ws.d2[b] = d2;

@@ -27,5 +27,5 @@ void launch_node_eval(const Params &P, const NodeEvalArgs &A, cudaStream_t st);
 int prepare_backward();
 void launch_backward(const Params &P, cudaStream_t st);
 // ffmpc_launch_fwd.cu
-void launch_forward(const Params &P, int it, cudaStream_t st);
+void launch_forward(const Params &P, int it, int lgA, cudaStream_t st);
 }  // namespace ffmpc

@@ -215,6 +215,9 @@ inline int __all_sync(unsigned, int p) {
   const unsigned full = emu::warp_width(w) == 32 ? 0xffffffffu : ((1u << emu::warp_width(w)) - 1u);
   return emu::ballot(p) == full;
 }
+inline double rsqrt(double x) { return 1.0 / std::sqrt(x); }
+inline int __ffs(int v) { return __builtin_ffs(v); }
+inline int __popc(unsigned v) { return __builtin_popcount(v); }
 inline int atomicAdd(int *a, int v) {
   int o = *a;
   *a += v;
