@@ -394,23 +394,59 @@ FFMPC_DEV bool dist_boxqp7(const ffmpc_config &cfg, const double *hrow, double q
 // Fx^T V Fx etc. are evaluated in the factored form of DESIGN.md section "Backward kernel".
 // The 7x7 gain algebra (LLT / BoxQP) is row-distributed over lanes 0..6 (dist_* above).
 // ------------------------------------------------------------------------------------------------
+constexpr int RS = 10;  // row stride (doubles) of the 21x7 operand arrays: 16-byte aligned rows for 128-bit broadcast loads,
+                        // and 80-byte stride so that a quarter-warp's 128-bit row stores hit 8 distinct bank groups
 template <bool FF> struct BwdLayout {
   static constexpr int n = FF ? 21 : 14;
   static constexpr int LD = FF ? 21 : 15;  // odd leading dimension: conflict-free column AND row reads
   static constexpr int oREC = 0;
   static constexpr int oV = oREC + REC_SIZE;
   static constexpr int oVE = oV + n * LD + (n * LD) % 2;
-  static constexpr int oYS = oVE + n * 8;
-  static constexpr int oGT = oYS + n * 8;
-  static constexpr int oQXU = oGT + n * 8;
-  static constexpr int oSS = oQXU + n * 8;
-  static constexpr int oLL = oSS + 56;   // Cholesky factor rows
-  static constexpr int oHI = oLL + 56;   // (masked) inverse of Quu, rows
-  static constexpr int oVX = oHI + 56;
+  static constexpr int oYS = oVE + n * RS;
+  static constexpr int oGT = oYS + n * RS;
+  static constexpr int oQXU = oGT + n * RS;
+  static constexpr int oSS = oQXU + n * RS;
+  static constexpr int oLL = oVE;        // Cholesky factor rows: aliases VE (dead once Qxu is formed)
+  static constexpr int oHI = oSS;        // masked inverse of Quu: aliases S (dead once Y and Quu are formed)
+  static constexpr int oVX = oSS + 56;
   static constexpr int oFS = oVX + 24;
   static constexpr int oDI = oFS + 24;   // reciprocal pivots
-  static constexpr int TOTAL = oDI + 8;  // doubles per warp
+  static constexpr int TOTAL = oDI + 8;  // doubles per warp (even: every warp region stays 16-byte aligned)
+  static_assert(n * RS >= 56 && TOTAL % 2 == 0 && oVE % 2 == 0, "layout");
 };
+
+struct alignas(16) dbl2 { double x, y; };
+// 7-vector rows in shared memory, moved as four 128-bit accesses (element 7 is padding)
+FFMPC_DEV void st7(double *row, const double *v) {
+  dbl2 *r = reinterpret_cast<dbl2 *>(row);
+  dbl2 a; a.x = v[0]; a.y = v[1]; r[0] = a;
+  a.x = v[2]; a.y = v[3]; r[1] = a;
+  a.x = v[4]; a.y = v[5]; r[2] = a;
+  a.x = v[6]; a.y = 0.0; r[3] = a;
+}
+FFMPC_DEV void ld7(const double *row, double *v) {
+  const dbl2 *r = reinterpret_cast<const dbl2 *>(row);
+  const dbl2 a = r[0], b2 = r[1], c2 = r[2], d = r[3];
+  v[0] = a.x; v[1] = a.y; v[2] = b2.x; v[3] = b2.y; v[4] = c2.x; v[5] = c2.y; v[6] = d.x;
+}
+// node record of knot t -> shared memory, asynchronously (LDGSTS, 16 bytes per copy): issued right after the last
+// read of the current record so that the load overlaps the gain computation and the value-function update
+FFMPC_DEV void rec_prefetch(double *dst, const double *src, int lane) {
+#if defined(FFMPC_EMU)
+  for (int i = lane; i < REC_SIZE; i += 32) dst[i] = src[i];
+#else
+  const unsigned d0 = (unsigned)__cvta_generic_to_shared(dst);
+  for (int i = lane; i < REC_SIZE / 2; i += 32)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 16u * (unsigned)i), "l"(src + 2 * i) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+}
+FFMPC_DEV void rec_wait() {
+#if !defined(FFMPC_EMU)
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
+  __syncwarp();
+}
 
 template <bool FF>
 FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, bool feasible, double &dg_out, double &dq_out) {
@@ -464,11 +500,12 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     }
   }
   __syncwarp();
+  rec_prefetch(REC, recb + (size_t)(N - 1) * REC_SIZE, lane);
+  if (act) FS[lane] = fsb[(N - 1) * n + lane];
 
   for (int t = N - 1; t >= 0; --t) {
-    for (int i = lane; i < REC_SIZE; i += 32) REC[i] = recb[(size_t)t * REC_SIZE + i];
-    if (act) FS[lane] = fsb[t * n + lane];
-    __syncwarp();
+    const double fs_next = (act && t > 0) ? fsb[(t - 1) * n + lane] : 0.0;
+    rec_wait();
     const double *G = REC + REC_G;
     // (a) Gh[:,c] = dt * G[:,c] ; (b) VE = V Et : row c
     double g[NJ], ve[NJ];
@@ -476,16 +513,16 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     for (int k = 0; k < NJ; ++k) {
       g[k] = dt * G[k * NZ + c];
       ve[k] = dt * V[k * LD + c] + V[(NJ + k) * LD + c];
-      if (act) {
-        VEs[c * 8 + k] = ve[k];
-        GT[c * 8 + k] = g[k];
-      }
+    }
+    if (act) {
+      st7(VEs + c * RS, ve);
+      st7(GT + c * RS, g);
     }
     __syncwarp();
     // (c) S = Et^T V Et
     for (int e = lane; e < 49; e += 32) {
       const int k = e / NJ, l = e - k * NJ;
-      SS[k * 8 + l] = dt * VEs[k * 8 + l] + VEs[(NJ + k) * 8 + l];
+      SS[k * 8 + l] = dt * VEs[k * RS + l] + VEs[(NJ + k) * RS + l];
     }
     __syncwarp();
     // (d) Tt = Pt^T V Et (row c), Y = Tt + Gh^T S (row c)
@@ -504,10 +541,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int k = 0; k < NJ; ++k)
 #pragma unroll
         for (int l = 0; l < NJ; ++l) y[l] += g[k] * SS[k * 8 + l];
-      if (act) {
-#pragma unroll
-        for (int k = 0; k < NJ; ++k) YS[c * 8 + k] = y[k];
-      }
+      if (act) st7(YS + c * RS, y);
       // (g) Qxu row c (classical: Lxu + Y Gu)
       if (!FF) {
 #pragma unroll
@@ -515,7 +549,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
           double s = REC[REC_LZZ + sym_idx(c, 2 * NJ + a)];
 #pragma unroll
           for (int k = 0; k < NJ; ++k) s += y[k] * (dt * G[k * NZ + 2 * NJ + a]);
-          if (act) QXU[c * 8 + a] = s;
+          if (act) QXU[c * RS + a] = s;
         }
       }
     }
@@ -536,8 +570,8 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
         if (c >= NJ && c < 2 * NJ) pc += dt * V[(2 * NJ + a) * LD + c - NJ];
         if (c >= 2 * NJ) pc *= alpha;
 #pragma unroll
-        for (int k = 0; k < NJ; ++k) pc += g[k] * VEs[(2 * NJ + a) * 8 + k];
-        if (act) QXU[c * 8 + a] = beta * pc;
+        for (int k = 0; k < NJ; ++k) pc += g[k] * VEs[(2 * NJ + a) * RS + k];
+        if (act) QXU[c * RS + a] = beta * pc;
       }
     }
     // (h) Quu row r7 (+ preg on the diagonal), Qu[r7]  -- lanes 0..6, the others shadow row 6
@@ -583,10 +617,15 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       if (i >= NJ && i < 2 * NJ) acc += dt * qxx[i - NJ];
       if (FF && i >= 2 * NJ) acc *= alpha;
       acc += LZZ_AT(i);
+      double yr[NJ], gr[NJ];
+      ld7(YS + i * RS, yr);
+      ld7(GT + i * RS, gr);
 #pragma unroll
-      for (int k = 0; k < NJ; ++k) acc += YS[i * 8 + k] * g[k] + GT[i * 8 + k] * tt[k];
+      for (int k = 0; k < NJ; ++k) acc += yr[k] * g[k] + gr[k] * tt[k];
       qxx[i] = acc;
     }
+    __syncwarp();  // every lane is done with this knot's record
+    if (t > 0) rec_prefetch(REC, recb + (size_t)(t - 1) * REC_SIZE, lane);
     // (i) gains.  LLT path (crocoddyl computeGains: Quu_llt.solve): factor row-distributed, then lane c solves
     //     Quu K[:,c] = Qxu[c,:]^T by substitution with the factor broadcast from shared memory; lane n does the same
     //     for Qu.  BoxQP path: K = (Quu_ff)^-1 Qxu^T with the masked inverse, k = -x*.
@@ -602,12 +641,12 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
         DI[lane] = dinv;
       }
       __syncwarp();
-      if (!okc) return false;
+      if (!okc) { rec_wait(); return false; }
       double quv[NJ];
       gather7(qu, quv);
 #pragma unroll
       for (int i = 0; i < NJ; ++i) {
-        double s2 = (lane == n) ? quv[i] : QXU[c * 8 + i];
+        double s2 = (lane == n) ? quv[i] : QXU[c * RS + i];
 #pragma unroll
         for (int k = 0; k < i; ++k) s2 -= LL[i * 8 + k] * kc[k];
         kc[i] = s2 * DI[i];
@@ -630,7 +669,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       const double lb = -cfg.tau_limits[r7] - u0, ub = cfg.tau_limits[r7] - u0;
       double xq = kb[t * NJ + r7];  // warm start = stored k_t (crocoddyl passes k_[t])
       unsigned mask;
-      if (!dist_boxqp7(cfg, qrow, qu, lb, ub, xq, lane, LL, DI, mask, hi)) return false;
+      if (!dist_boxqp7(cfg, qrow, qu, lb, ub, xq, lane, LL, DI, mask, hi)) { rec_wait(); return false; }
       kv = -xq;
       if (!((mask >> r7) & 1u)) qu = 0.0;  // clamped directions do not count for the stopping measure
       __syncwarp();
@@ -643,7 +682,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int a = 0; a < NJ; ++a) kc[a] = 0.0;
 #pragma unroll
       for (int bb = 0; bb < NJ; ++bb) {
-        const double qb = QXU[c * 8 + bb];
+        const double qb = QXU[c * RS + bb];
 #pragma unroll
         for (int a = 0; a < NJ; ++a) kc[a] += HI[a * 8 + bb] * qb;
       }
@@ -669,8 +708,10 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
 #pragma unroll
     for (int i = 0; i < n; ++i) {
       double s = qxx[i];
+      double qr[NJ];
+      ld7(QXU + i * RS, qr);
 #pragma unroll
-      for (int a = 0; a < NJ; ++a) s -= QXU[i * 8 + a] * kc[a];
+      for (int a = 0; a < NJ; ++a) s -= qr[a] * kc[a];
       qxx[i] = s;
       if (act) V[i * LD + c] = s;
     }
@@ -697,8 +738,12 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       dg -= warp_sum(act ? vx * FS[c] : 0.0);
       dq += warp_sum(act ? vf * FS[c] : 0.0);
     }
-    if (__any_sync(0xffffffffu, bad && act)) return false;
+    if (__any_sync(0xffffffffu, bad && act)) {
+      rec_wait();
+      return false;
+    }
     __syncwarp();
+    if (act) FS[lane] = fs_next;
   }
 #undef LZZ_AT
   dg_out = dg;
@@ -711,7 +756,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const __grid_constant__ Par
 #ifdef FFMPC_EMU
   double *smem = (double *)emu::S().smem;
 #else
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
 #endif
   const Workspace &ws = P.ws;
   const int warp = (int)(threadIdx.x >> 5), lane = (int)(threadIdx.x & 31);
