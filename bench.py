@@ -155,17 +155,37 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_baseline(args, cfg, model, inp, sample: int, nthreads: int) -> dict:
-    """The oracle port timed on the host cores, bounded sample of the same workload."""
+def _cpu_rate_probe(args, cfg, model, inp, lib, nthreads: int) -> float:
+    """solves/s of the CPU port on a tiny probe (4 instances per thread), used to size the timed sample."""
+    from oracle import oracle as orc
+
+    n = min(inp.B, 4 * nthreads)
+    sub = inp.slice(np.arange(n))
+    t0 = time.perf_counter()
+    orc.solve_batch(cfg, model, sub, args.iters, True, nthreads=nthreads, _use=lib)
+    return n / max(time.perf_counter() - t0, 1e-6)
+
+
+def _cpu_sample_size(args, rate: float, seconds: float, B: int, nthreads: int) -> int:
+    if args.cpu_sample:
+        return min(args.cpu_sample, B)
+    n = int(rate * seconds)
+    n = max(nthreads, (n // nthreads) * nthreads)
+    return min(n, B)
+
+
+def cpu_baseline(args, cfg, model, inp, nthreads: int) -> dict:
+    """The oracle port timed on the host cores: a bounded sample (about 15 s of CPU work) of the same workload."""
     from oracle import oracle as orc
 
     lib, how = orc.timing_lib()
-    sub = inp.slice(np.arange(min(sample, inp.B)))
+    rate = _cpu_rate_probe(args, cfg, model, inp, lib, nthreads)
+    sub = inp.slice(np.arange(_cpu_sample_size(args, rate, 15.0, inp.B, nthreads)))
     t0 = time.perf_counter()
     orc.solve_batch(cfg, model, sub, args.iters, True, nthreads=nthreads, _use=lib)
     dt = time.perf_counter() - t0
     return {"value": sub.B / dt, "unit": UNIT, "cores": nthreads, "kind": "port",
-            "sample": f"{sub.B} instances of the same batch, {args.iters} fixed iterations, oracle/ffmpc_oracle.cpp ({how}), "
+            "sample": f"first {sub.B} instances of the same batch, {args.iters} fixed iterations, oracle/ffmpc_oracle.cpp ({how}), "
                       f"{nthreads} threads over instances, {dt:.1f} s",
             "note": "reference's own CPU path (Crocoddyl/Pinocchio via Python) is not installable on this box"}
 
@@ -173,11 +193,15 @@ def cpu_baseline(args, cfg, model, inp, sample: int, nthreads: int) -> dict:
 def run_reference(args, rank: int, world: int):
     if rank != 0:
         return
-    cfg, model, inp, nx = make_problem(args, 0, args.cpu_sample or 4 * (os.cpu_count() or 1))
     from oracle import oracle as orc
 
     lib, how = orc.timing_lib()
     nthreads = os.cpu_count() or 1
+    cfg, model, probe_inp, nx = make_problem(args, 0, 4 * nthreads)
+    rate = _cpu_rate_probe(args, cfg, model, probe_inp, lib, nthreads)
+    # each step = a bounded sample (about 8 s of CPU work) of the b200 arm's per-GPU batch
+    n = _cpu_sample_size(args, rate, 8.0, args.batch, nthreads)
+    cfg, model, inp, nx = make_problem(args, 0, n)
     for _ in range(args.warmup):
         orc.solve_batch(cfg, model, inp.slice(np.arange(min(nthreads, inp.B))), args.iters, True, nthreads=nthreads, _use=lib)
     t0 = time.perf_counter()
@@ -190,7 +214,7 @@ def run_reference(args, rank: int, world: int):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, inp.B, nx),
+        "config": workload_config(args, args.batch, nx),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -379,7 +403,7 @@ def main():
     cpu = None
     if not args.no_cpu_baseline:
         nthreads = os.cpu_count() or 1
-        cpu = cpu_baseline(args, cfg, model, inp, args.cpu_sample or 4 * nthreads, nthreads)
+        cpu = cpu_baseline(args, cfg, model, inp, nthreads)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
