@@ -1,0 +1,396 @@
+// ffmpc_coop_kernels.cuh -- kernels built on the lane-cooperative knot evaluation of ffmpc_coop.cuh:
+//   k_node_diff_coop : octet (8 lanes) per (instance, knot)   ShootingProblem.calc + calcDiff -> records, gaps
+//   k_forward_coop   : octet per instance                      forwardPass + sequential line search + acceptance
+//   k_node_eval_coop : octet per evaluation point              parity-test hook (records -> k_node_expand -> dense)
+// Block = 128 threads = 16 octets; dynamic shared memory = constant table + 16 octet scratch areas.
+#pragma once
+
+#include "ffmpc_coop.cuh"
+#include "ffmpc_kernels.cuh"
+
+namespace ffmpc {
+
+constexpr int kCoopBlock = 128;
+constexpr size_t kCoopSmemBytes = (size_t)(CT_SIZE + (kCoopBlock / 8) * CS_SIZE) * sizeof(double);
+
+FFMPC_DEV double *coop_smem_base() {
+#ifdef FFMPC_EMU
+  return (double *)emu::S().smem;
+#else
+  extern __shared__ __align__(16) double coop_dyn_smem[];
+  return coop_dyn_smem;
+#endif
+}
+
+// ------------------------------------------------------------------------------------------------
+template <int NC, bool FF>
+__global__ void __launch_bounds__(kCoopBlock) k_node_diff_coop(const __grid_constant__ Params P) {
+  const Workspace &ws = P.ws;
+  constexpr int nx = FF ? 21 : 14;
+  double *ct = coop_smem_base();
+  double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
+  coop_fill_table(P.mdl, P.cfg, ct);
+  __syncthreads();
+  const int N = ws.N;
+  const int g = global_tid();
+  const int o = g >> 3, j = g & 7;
+  const int jj = j < NJ ? j : NJ - 1;
+  const bool act = j < NJ;
+  const int nfree = ws.counts[0];
+  const int base = (NC == 0) ? 0 : nfree;
+  const int cnt = (NC == 0) ? nfree : ws.counts[1];
+  int slot = o / (N + 1), t = o - slot * (N + 1);
+  bool valid = slot < cnt;
+  if (!valid) { slot = 0; t = 0; }
+  if (cnt == 0) return;
+  const int b = ws.perm[base + slot];
+  if (valid && (ws.done[b] || !ws.recalc[b])) valid = false;
+  if (!__any_sync(kFull, valid)) return;
+  const size_t bufoff = (size_t)ws.cur[b] * ws.B;
+  const double *xg = ws.xs + ((bufoff + b) * (N + 1) + t) * nx;
+  CoopX x, xn;
+  x.q = xg[jj];
+  x.v = xg[NJ + jj];
+  x.t = FF ? xg[2 * NJ + jj] : 0.0;
+  const double u = (t < N) ? ws.us[((bufoff + b) * N + t) * NJ + jj] : 0.0;
+  CoopCtx ctx;
+  ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
+  ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
+  ctx.xr_q = ws.x_reg_ref[(size_t)b * 14 + jj];
+  ctx.xr_v = ws.x_reg_ref[(size_t)b * 14 + NJ + jj];
+  ctx.tau_ref = ws.tau_ref[(size_t)b * NJ + jj];
+  const double *x0 = ws.x0 + (size_t)b * nx;
+  ctx.yr_q = x0[jj];
+  ctx.yr_v = x0[NJ + jj];
+  ctx.yr_t = FF ? x0[2 * NJ + jj] : 0.0;
+  ctx.terminal = (t == N);
+  double cost, lam[3];
+  double *rec = ws.rec + ((size_t)b * (N + 1) + t) * REC_SIZE;
+  coop_action_node<NC, FF, true>(P.mdl, P.cfg, ct, sm, j, ctx, x, u, xn, cost, lam, rec, valid);
+  if (!valid) return;
+  if (j == 0) {
+    ws.ncost[(size_t)b * (N + 1) + t] = cost;
+    if (NC != 0 && t < 2) {
+      ws.f_pred[b * 6 + t * 3 + 0] = lam[0];
+      ws.f_pred[b * 6 + t * 3 + 1] = lam[1];
+      ws.f_pred[b * 6 + t * 3 + 2] = lam[2];
+    }
+  }
+  if (!act) return;
+  // gaps: fs[0] = x0 - xs[0]; fs[t+1] = xnext_t - xs[t+1]
+  double *fsb = ws.fs + (size_t)b * (N + 1) * nx;
+  if (t == 0) {
+    fsb[j] = x0[j] - x.q;
+    fsb[NJ + j] = x0[NJ + j] - x.v;
+    if (FF) fsb[2 * NJ + j] = x0[2 * NJ + j] - x.t;
+  }
+  if (t < N) {
+    const double *xnx = xg + nx;
+    double *f = fsb + (size_t)(t + 1) * nx;
+    f[j] = xn.q - xnx[j];
+    f[NJ + j] = xn.v - xnx[NJ + j];
+    if (FF) f[2 * NJ + j] = xn.t - xnx[2 * NJ + j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update.
+// One octet per instance; the step lengths 1, 1/2, ... are tried in order (the loop of SolverFDDP::solve) into the
+// single trial slot 1 - cur; the warp leaves the loop when all of its four instances have accepted.
+// ------------------------------------------------------------------------------------------------
+template <int NC, bool FF>
+__global__ void __launch_bounds__(kCoopBlock) k_forward_coop(const __grid_constant__ Params P, int it) {
+  const Workspace &ws = P.ws;
+  const ffmpc_config &cfg = P.cfg;
+  constexpr int nx = FF ? 21 : 14;
+  double *ct = coop_smem_base();
+  double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
+  coop_fill_table(P.mdl, P.cfg, ct);
+  __syncthreads();
+  const int N = ws.N;
+  const int g = global_tid();
+  const int o = g >> 3, j = g & 7;
+  const int jj = j < NJ ? j : NJ - 1;
+  const bool act = j < NJ;
+  const int lane = (int)(threadIdx.x & 31);
+  const unsigned omask = 0xffu << (lane & ~7);
+  const int nfree = ws.counts[0];
+  const int base = (NC == 0) ? 0 : nfree;
+  const int cnt = (NC == 0) ? nfree : ws.counts[1];
+  if (cnt == 0) return;
+  bool valid = o < cnt;
+  const int b = ws.perm[base + (valid ? o : 0)];
+  if (valid && ws.done[b]) valid = false;
+  if (!__any_sync(kFull, valid)) return;
+  const int cur = ws.cur[b];
+  const int trial = 1 - cur;
+  const bool feasible = ws.feas[b] != 0;
+  double cost = ws.cost[b];
+  if (!ws.cost_valid[b]) {
+    cost = 0.0;  // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
+    for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
+  }
+  const double dg = ws.dg[b], dq = ws.dq[b];
+  const double *xs = ws.xs + ((size_t)cur * ws.B + b) * (N + 1) * nx;
+  const double *us = ws.us + ((size_t)cur * ws.B + b) * N * NJ;
+  double *xt_all = ws.xs + ((size_t)trial * ws.B + b) * (N + 1) * nx;
+  double *ut_all = ws.us + ((size_t)trial * ws.B + b) * N * NJ;
+  const double *fs = ws.fs + (size_t)b * (N + 1) * nx;
+  const double *Vfs = ws.Vfs + (size_t)b * (N + 1) * nx;
+  const double *Kb = ws.K + (size_t)b * N * NJ * nx;
+  const double *kb = ws.k + (size_t)b * N * NJ;
+  const double *x0 = ws.x0 + (size_t)b * nx;
+  CoopCtx ctx;
+  ctx.xr_q = ws.x_reg_ref[(size_t)b * 14 + jj];
+  ctx.xr_v = ws.x_reg_ref[(size_t)b * 14 + NJ + jj];
+  ctx.tau_ref = ws.tau_ref[(size_t)b * NJ + jj];
+  ctx.yr_q = x0[jj];
+  ctx.yr_v = x0[NJ + jj];
+  ctx.yr_t = FF ? x0[2 * NJ + jj] : 0.0;
+  const double ulim = ct[jj * CT_STRIDE + CT_TAULIM];
+
+  double d1 = 0.0, d2 = 0.0, cost_try = 0.0;  // of the latest rollout that did not throw
+  double lam01[6] = {NAN, NAN, NAN, NAN, NAN, NAN};
+  int ia_ok = -1, ia_acc = -1;
+  for (int ia = 0; ia < cfg.n_alphas; ++ia) {
+    const bool has = valid && ia_acc < 0;
+    if (!__any_sync(kFull, has)) break;
+    const double steplength = ldexp(1.0, -ia);
+    const bool close = feasible || (steplength == 1.0);
+    // ---- rollout ----
+    CoopX xh;
+    xh.q = ctx.yr_q; xh.v = ctx.yr_v; xh.t = ctx.yr_t;  // x0
+    double ct_sum = 0.0, dv_part = 0.0;
+    bool failed = false;
+    for (int t = 0; t <= N; ++t) {
+      CoopX xt;
+      const double *fst = fs + (size_t)t * nx, *xst = xs + (size_t)t * nx, *vft = Vfs + (size_t)t * nx;
+      xt.q = close ? xh.q : xh.q + fst[jj] * (steplength - 1.0);
+      xt.v = close ? xh.v : xh.v + fst[NJ + jj] * (steplength - 1.0);
+      xt.t = FF ? (close ? xh.t : xh.t + fst[2 * NJ + jj] * (steplength - 1.0)) : 0.0;
+      const double dxq = xt.q - xst[jj], dxv = xt.v - xst[NJ + jj], dxt = FF ? xt.t - xst[2 * NJ + jj] : 0.0;
+      if (has && act) {
+        double *xw = xt_all + (size_t)t * nx;
+        xw[j] = xt.q;
+        xw[NJ + j] = xt.v;
+        if (FF) xw[2 * NJ + j] = xt.t;
+        dv_part += vft[j] * dxq + vft[NJ + j] * dxv + (FF ? vft[2 * NJ + j] * dxt : 0.0);  // -fs_t^T Vxx_t (xs_t - xs_try_t)
+      }
+      double u = 0.0;
+      if (t < N) {
+        // K dx: lane j multiplies its own three columns of every row, reduce-scatter gives row a to lane a
+        double pr[8];
+        const double *Kt = Kb + (size_t)t * NJ * nx;
+#pragma unroll
+        for (int a = 0; a < NJ; ++a) {
+          double s = Kt[a * nx + jj] * dxq + Kt[a * nx + NJ + jj] * dxv;
+          if (FF) s += Kt[a * nx + 2 * NJ + jj] * dxt;
+          pr[a] = act ? s : 0.0;
+        }
+        pr[7] = 0.0;
+        const double kd = oct_reduce_scatter8(pr, j);
+        double s = us[t * NJ + jj] - kb[t * NJ + jj] * steplength;
+        s -= kd;
+        if (cfg.use_box_fddp) s = fmin(fmax(s, -ulim), ulim);
+        u = s;
+        if (has && act) ut_all[t * NJ + j] = s;
+      }
+      ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
+      ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
+      ctx.terminal = (t == N);
+      double cst, lam[3];
+      coop_action_node<NC, FF, false>(P.mdl, cfg, ct, sm, j, ctx, xt, u, xh, cst, lam, nullptr, false);
+      if (NC != 0 && t < 2 && has && !failed) {
+        lam01[t * 3 + 0] = lam[0];
+        lam01[t * 3 + 1] = lam[1];
+        lam01[t * 3 + 2] = lam[2];
+      }
+      ct_sum += cst;
+      bool bad = false;
+      if (t < N) bad = act && !(isfinite(xh.q) && isfinite(xh.v) && isfinite(xh.t));
+      const bool anybad = (__ballot_sync(kFull, bad) & omask) != 0u;
+      if (!isfinite(ct_sum) || anybad) failed = true;  // "forward_error": this step length is skipped
+    }
+    const double dv_all = oct_sum(dv_part);  // unconditional: every lane of the warp takes part in the shuffles
+    const double dv = feasible ? 0.0 : dv_all;
+    if (has && !failed) {
+      cost_try = ct_sum;
+      ia_ok = ia;
+      const double dV = cost - ct_sum;
+      d1 = dg + dv;
+      d2 = dq - 2.0 * dv;
+      const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
+      bool acc;
+      if (dVexp >= 0.0) acc = (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp);
+      else acc = (!feasible && dV > cfg.th_acceptnegstep * dVexp);
+      if (acc) ia_acc = ia;
+    }
+  }
+  if (!valid || j != 0) return;
+  const bool accepted = ia_acc >= 0;
+  if (NC != 0) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+      if (!isnan(lam01[i]) || accepted) ws.f_pred[b * 6 + i] = lam01[i];
+  }
+  if (!accepted && ia_ok < 0) {
+    d1 = ws.d1[b];
+    d2 = ws.d2[b];
+  }
+  const double steplength = accepted ? ldexp(1.0, -ia_acc) : ldexp(1.0, -(cfg.n_alphas - 1));
+  double preg = ws.preg[b];
+  int wasfeas = ws.wasfeas[b];
+  if (accepted) {
+    wasfeas = feasible ? 1 : 0;
+    ws.wasfeas[b] = wasfeas;
+    ws.feas[b] = (wasfeas || steplength == 1.0) ? 1 : 0;
+    ws.cur[b] = trial;
+    cost = cost_try;
+    ws.recalc[b] = 1;
+  } else {
+    ws.recalc[b] = 0;
+  }
+  ws.cost_valid[b] = 1;
+  ws.cost[b] = cost;
+  ws.d1[b] = d1;
+  ws.d2[b] = d2;
+  bool finished = false;
+  int okflag = 0;
+  if (steplength > cfg.th_stepdec) {
+    preg /= cfg.reg_decfactor;
+    if (preg < cfg.reg_min) preg = cfg.reg_min;
+  }
+  if (steplength <= cfg.th_stepinc) {
+    preg *= cfg.reg_incfactor;
+    if (preg > cfg.reg_max) preg = cfg.reg_max;
+    if (preg == cfg.reg_max) finished = true;
+  }
+  ws.preg[b] = preg;
+  if (!finished) {
+    const double stop = fabs(d1 + 0.5 * d2);
+    ws.stop[b] = stop;
+    if (!ws.fixed_iters && wasfeas && stop < cfg.th_stop) {
+      finished = true;
+      okflag = 1;
+    }
+  }
+  if (finished) {
+    ws.done[b] = 1;
+    ws.ok[b] = okflag;
+    ws.iter[b] = it;
+  } else {
+    ws.iter[b] = it + 1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// parity-test hook: ActionModel.calc + calcDiff at arbitrary points.  The cooperative kernel writes the knot record
+// (A.rec, zero-initialised by the host), k_node_expand turns it into the dense Crocoddyl-shaped matrices.
+// ------------------------------------------------------------------------------------------------
+struct NodeEvalCoopArgs {
+  NodeEvalArgs a;
+  double *rec;  // [M, REC_SIZE]
+};
+template <int NC, bool FF>
+__global__ void __launch_bounds__(kCoopBlock) k_node_eval_coop(const __grid_constant__ Params P, NodeEvalCoopArgs AA) {
+  const Workspace &ws = P.ws;
+  const NodeEvalArgs &A = AA.a;
+  constexpr int nx = FF ? 21 : 14;
+  double *ct = coop_smem_base();
+  double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
+  coop_fill_table(P.mdl, P.cfg, ct);
+  __syncthreads();
+  const int N = ws.N;
+  const int g = global_tid();
+  int m = g >> 3;
+  const int j = g & 7;
+  const int jj = j < NJ ? j : NJ - 1;
+  bool valid = m < A.M;
+  if (!valid) m = 0;
+  const int b = A.inst[m], t = A.knot[m];
+  const int nc_b = (ws.mode[b] == FFMPC_MODE_CONTACT) ? P.cfg.contact_nc : 0;
+  if (nc_b != NC) valid = false;
+  if (!__any_sync(kFull, valid)) return;
+  CoopX x, xn;
+  x.q = A.x[(size_t)m * nx + jj];
+  x.v = A.x[(size_t)m * nx + NJ + jj];
+  x.t = FF ? A.x[(size_t)m * nx + 2 * NJ + jj] : 0.0;
+  const double u = A.u[(size_t)m * NJ + jj];
+  CoopCtx ctx;
+  ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
+  ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
+  ctx.xr_q = ws.x_reg_ref[(size_t)b * 14 + jj];
+  ctx.xr_v = ws.x_reg_ref[(size_t)b * 14 + NJ + jj];
+  ctx.tau_ref = ws.tau_ref[(size_t)b * NJ + jj];
+  const double *x0 = ws.x0 + (size_t)b * nx;
+  ctx.yr_q = x0[jj];
+  ctx.yr_v = x0[NJ + jj];
+  ctx.yr_t = FF ? x0[2 * NJ + jj] : 0.0;
+  ctx.terminal = (t == N);
+  double cost, lam[3];
+  coop_action_node<NC, FF, true>(P.mdl, P.cfg, ct, sm, j, ctx, x, u, xn, cost, lam, AA.rec + (size_t)m * REC_SIZE, valid);
+  if (!valid) return;
+  if (j == 0) {
+    if (A.cost) A.cost[m] = cost;
+    if (A.force) for (int i = 0; i < 3; ++i) A.force[(size_t)m * 3 + i] = lam[i];
+  }
+  if (j < NJ && A.xnext) {
+    A.xnext[(size_t)m * nx + j] = xn.q;
+    A.xnext[(size_t)m * nx + NJ + j] = xn.v;
+    if (FF) A.xnext[(size_t)m * nx + 2 * NJ + j] = xn.t;
+  }
+}
+
+template <bool FF>
+__global__ void k_node_expand(const __grid_constant__ Params P, NodeEvalCoopArgs AA) {
+  const Workspace &ws = P.ws;
+  const NodeEvalArgs &A = AA.a;
+  constexpr int nx = FF ? 21 : 14;
+  const int m = global_tid();
+  if (m >= A.M) return;
+  const int t = A.knot[m];
+  const double *rec = AA.rec + (size_t)m * REC_SIZE;
+  const double dt = P.cfg.dt_ocp;
+  const double alpha = fmin(fmax(P.cfg.ff_alpha, 0.0), 0.999999), beta = 1.0 - alpha;
+  const bool running = FF || (t != ws.N);
+  for (int i = 0; i < nx; ++i) {
+    for (int j = 0; j < nx; ++j) {
+      double fx = (i == j) ? 1.0 : 0.0;
+      if (i < 14) {
+        const int r = i % NJ;
+        const double sc = (i < NJ) ? dt * dt : dt;
+        if (running) {
+          fx += sc * rec[REC_G + r * NZ + j];
+          if (i < NJ && j == NJ + i) fx += dt;
+        }
+        if (j >= 14) fx = running ? sc * rec[REC_G + r * NZ + j] : 0.0;
+      } else {
+        fx = (i == j) ? alpha : 0.0;
+      }
+      if (A.Fx) A.Fx[((size_t)m * nx + i) * nx + j] = fx;
+      if (A.Lxx) A.Lxx[((size_t)m * nx + i) * nx + j] = rec[REC_LZZ + sym_idx_any(i, j)];
+    }
+    for (int a = 0; a < NJ; ++a) {
+      double fu, lxu;
+      if (FF) {
+        fu = (i == 14 + a) ? beta : 0.0;
+        lxu = 0.0;
+      } else {
+        const int r = i % NJ;
+        const double sc = (i < NJ) ? dt * dt : dt;
+        fu = running ? sc * rec[REC_G + r * NZ + 14 + a] : 0.0;
+        lxu = rec[REC_LZZ + sym_idx_any(i, 14 + a)];
+      }
+      if (A.Fu) A.Fu[((size_t)m * nx + i) * NJ + a] = fu;
+      if (A.Lxu) A.Lxu[((size_t)m * nx + i) * NJ + a] = lxu;
+    }
+    if (A.Lx) A.Lx[(size_t)m * nx + i] = rec[REC_LZ + i];
+  }
+  for (int a = 0; a < NJ; ++a) {
+    if (A.Lu) A.Lu[(size_t)m * NJ + a] = FF ? rec[REC_LW + a] : rec[REC_LZ + 14 + a];
+    for (int c = 0; c < NJ; ++c)
+      if (A.Luu) A.Luu[((size_t)m * NJ + a) * NJ + c] = FF ? ((a == c) ? rec[REC_LWW + a] : 0.0) : rec[REC_LZZ + sym_idx_any(14 + a, 14 + c)];
+  }
+}
+
+}  // namespace ffmpc

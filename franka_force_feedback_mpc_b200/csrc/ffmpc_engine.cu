@@ -44,6 +44,7 @@ struct ffmpc_handle {
   int max_batch = 0;
   int N = 0, nx = 0;
   int lgA_max = 0;  // log2 of the line-search lanes per instance the trajectory slots were sized for
+  bool coop = true; // lane-cooperative knot evaluation (8 lanes per knot); FFMPC_COOP=0 selects the thread-per-knot kernels
   ffmpc_config cfg;
   ffmpc_model mdl;
   cudaStream_t stream = nullptr;
@@ -146,11 +147,22 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
   launches += 3;
   if (int e = mark(h, FFMPC_FAM_OTHER, 3)) return e;
   for (int it = 0; it < max_iters; ++it) {
-    launch_node_diff(P, st);
+#ifdef FFMPC_EMU
+    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: node_diff\n", it);
+#endif
+    if (h->coop) launch_node_diff_coop(P, st);
+    else launch_node_diff(P, st);
     if (int e = mark(h, FFMPC_FAM_NODE_DIFF, 2)) return e;
+#ifdef FFMPC_EMU
+    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: backward\n", it);
+#endif
     launch_backward(P, st);
     if (int e = mark(h, FFMPC_FAM_BACKWARD, 1)) return e;
-    launch_forward(P, it, std::min(h->lgA_max, fwd_lanes_log2(B, h->cfg.n_alphas)), st);
+#ifdef FFMPC_EMU
+    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: forward\n", it);
+#endif
+    if (h->coop) launch_forward_coop(P, it, st);
+    else launch_forward(P, it, std::min(h->lgA_max, fwd_lanes_log2(B, h->cfg.n_alphas)), st);
     if (int e = mark(h, FFMPC_FAM_FORWARD, 2)) return e;
     launches += 5;
   }
@@ -272,7 +284,8 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   DA(ws.perm, B);
   DA(ws.counts, 2);
   // parallel line search: A = 2^lgA lanes per instance, each with its own trial slot (see k_forward)
-  h->lgA_max = fwd_lanes_log2(max_batch, cfg->n_alphas);
+  if (const char *e = getenv("FFMPC_COOP")) h->coop = atoi(e) != 0;
+  h->lgA_max = h->coop ? 0 : fwd_lanes_log2(max_batch, cfg->n_alphas);
   ws.nslots = 1 + (1 << h->lgA_max);
   DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
   DA(ws.us, (size_t)ws.nslots * B * N * NJ);
@@ -291,9 +304,9 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
     ffmpc_destroy(h);
     return rc;
   }
-  if (prepare_backward() != 0) {
+  if (prepare_backward() != 0 || prepare_coop_node() != 0 || prepare_coop_fwd() != 0) {
     ffmpc_destroy(h);
-    return fail(FFMPC_ERR_CUDA, "cudaFuncSetAttribute(k_backward, MaxDynamicSharedMemorySize) failed");
+    return fail(FFMPC_ERR_CUDA, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed");
   }
   *out = h;
   return FFMPC_OK;
@@ -447,16 +460,19 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
   A.Fx = (double *)talloc(Ms * nx * nx * 8); A.Fu = (double *)talloc(Ms * nx * NJ * 8); A.Lx = (double *)talloc(Ms * nx * 8);
   A.Lu = (double *)talloc(Ms * NJ * 8); A.Lxx = (double *)talloc(Ms * nx * nx * 8); A.Lxu = (double *)talloc(Ms * nx * NJ * 8);
   A.Luu = (double *)talloc(Ms * NJ * NJ * 8);
+  double *d_rec = (double *)talloc(Ms * REC_SIZE * 8);
+  if (d_rec) cudaMemsetAsync(d_rec, 0, Ms * REC_SIZE * 8, st);
   for (void *p : tmp)
     if (!p) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
-  if (!din.mode || !A.Luu) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
+  if (!din.mode || !A.Luu || !d_rec) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
   if (int e = bind_inputs(h, &din, 0, 1)) { cleanup(); return e; }
   Params P;
   P.mdl = h->mdl;
   P.cfg = h->cfg;
   P.ws = h->ws;
   FFMPC_LAUNCH(k_init_state, (in->B + 127) / 128, 128, 0, st, P);  // resolves tau_ref
-  launch_node_eval(P, A, st);
+  if (h->coop) launch_node_eval_coop(P, A, d_rec, st);
+  else launch_node_eval(P, A, st);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess) { cleanup(); return fail(FFMPC_ERR_CUDA, std::string("node_eval launch: ") + cudaGetErrorString(le)); }
   auto down = [&](void *dst, const void *src, size_t bytes) { if (dst) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st); };

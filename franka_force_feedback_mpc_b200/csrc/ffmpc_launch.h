@@ -28,4 +28,10 @@ int prepare_backward();
 void launch_backward(const Params &P, cudaStream_t st);
 // ffmpc_launch_fwd.cu
 void launch_forward(const Params &P, int it, int lgA, cudaStream_t st);
+// ffmpc_launch_coop_node.cu / ffmpc_launch_coop_fwd.cu  (lane-cooperative knot evaluation, ffmpc_coop.cuh)
+int prepare_coop_node();
+int prepare_coop_fwd();
+void launch_node_diff_coop(const Params &P, cudaStream_t st);
+void launch_node_eval_coop(const Params &P, const NodeEvalArgs &A, double *rec, cudaStream_t st);
+void launch_forward_coop(const Params &P, int it, cudaStream_t st);
 }  // namespace ffmpc

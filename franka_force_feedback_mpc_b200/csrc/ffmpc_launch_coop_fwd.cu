@@ -1,0 +1,35 @@
+// k_forward_coop instantiations (octet per instance: rollout + sequential line search).
+#include "ffmpc_launch.h"
+#include "ffmpc_coop_kernels.cuh"
+
+namespace ffmpc {
+
+#ifdef FFMPC_EMU
+#define COOP_ATTR(k) 0
+#else
+#define COOP_ATTR(k) (cudaFuncSetAttribute((k), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCoopSmemBytes) != cudaSuccess)
+#endif
+
+int prepare_coop_fwd() {
+  int bad = 0;
+  bad |= COOP_ATTR((k_forward_coop<0, true>)); bad |= COOP_ATTR((k_forward_coop<1, true>)); bad |= COOP_ATTR((k_forward_coop<3, true>));
+  bad |= COOP_ATTR((k_forward_coop<0, false>)); bad |= COOP_ATTR((k_forward_coop<1, false>)); bad |= COOP_ATTR((k_forward_coop<3, false>));
+  return bad;
+}
+
+void launch_forward_coop(const Params &P, int it, cudaStream_t st) {
+  const int grid = (int)(((size_t)P.ws.B * 8 + kCoopBlock - 1) / kCoopBlock);
+  const bool ff = P.cfg.variant == FFMPC_VARIANT_FF;
+  const int nc = P.cfg.contact_nc;
+  if (ff) {
+    FFMPC_LAUNCH((k_forward_coop<0, true>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+    if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, true>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+    else FFMPC_LAUNCH((k_forward_coop<3, true>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+  } else {
+    FFMPC_LAUNCH((k_forward_coop<0, false>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+    if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, false>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+    else FFMPC_LAUNCH((k_forward_coop<3, false>), grid, kCoopBlock, kCoopSmemBytes, st, P, it);
+  }
+}
+
+}  // namespace ffmpc

@@ -208,6 +208,11 @@ template <class T> inline T __shfl_down_sync(unsigned, T v, unsigned d, int widt
   const int src = lane + (int)d;
   return emu::shfl_idx(v, (src / width == lane / width) ? src : lane);
 }
+template <class T> inline T __shfl_up_sync(unsigned, T v, unsigned d, int width = 32) {
+  const int lane = emu::S().cur % 32;
+  const int src = lane - (int)d;
+  return emu::shfl_idx(v, (src >= 0 && src / width == lane / width) ? src : lane);
+}
 inline unsigned __ballot_sync(unsigned, int p) { return emu::ballot(p); }
 inline int __any_sync(unsigned, int p) { return emu::ballot(p) != 0; }
 inline int __all_sync(unsigned, int p) {
