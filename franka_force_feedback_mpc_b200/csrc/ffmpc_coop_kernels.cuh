@@ -11,6 +11,9 @@
 namespace ffmpc {
 
 constexpr int kCoopBlock = 128;
+#ifndef FFMPC_COOP_MINBLOCKS
+#define FFMPC_COOP_MINBLOCKS 3  // resident blocks per SM the register allocation is sized for
+#endif
 constexpr size_t kCoopSmemBytes = (size_t)(CT_SIZE + (kCoopBlock / 8) * CS_SIZE) * sizeof(double);
 
 FFMPC_DEV double *coop_smem_base() {
@@ -24,25 +27,25 @@ FFMPC_DEV double *coop_smem_base() {
 
 // ------------------------------------------------------------------------------------------------
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock) k_node_diff_coop(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_coop(const __grid_constant__ Params P) {
   const Workspace &ws = P.ws;
   constexpr int nx = FF ? 21 : 14;
+  const int N = ws.N;
+  const int nfree = ws.counts[0];
+  const int base = (NC == 0) ? 0 : nfree;
+  const int cnt = (NC == 0) ? nfree : ws.counts[1];
+  if ((long long)blockIdx.x * (kCoopBlock / 8) >= (long long)cnt * (N + 1)) return;  // block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
   coop_fill_table(P.mdl, P.cfg, ct);
   __syncthreads();
-  const int N = ws.N;
   const int g = global_tid();
   const int o = g >> 3, j = g & 7;
   const int jj = j < NJ ? j : NJ - 1;
   const bool act = j < NJ;
-  const int nfree = ws.counts[0];
-  const int base = (NC == 0) ? 0 : nfree;
-  const int cnt = (NC == 0) ? nfree : ws.counts[1];
   int slot = o / (N + 1), t = o - slot * (N + 1);
   bool valid = slot < cnt;
   if (!valid) { slot = 0; t = 0; }
-  if (cnt == 0) return;
   const int b = ws.perm[base + slot];
   if (valid && (ws.done[b] || !ws.recalc[b])) valid = false;
   if (!__any_sync(kFull, valid)) return;
@@ -94,15 +97,24 @@ __global__ void __launch_bounds__(kCoopBlock) k_node_diff_coop(const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update.
-// One octet per instance; the step lengths 1, 1/2, ... are tried in order (the loop of SolverFDDP::solve) into the
-// single trial slot 1 - cur; the warp leaves the loop when all of its four instances have accepted.
+// k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update, ONE step
+// length per launch.  Pass `ia` rolls out alpha = 2^-ia for the instances still searching: pass 0 takes every live
+// instance of the mode bucket (ws.perm), pass ia > 0 takes the compacted queue written by pass ia - 1 (rejected
+// instances are appended with an atomic counter), so warps stay full of useful octets instead of waiting for the
+// slowest of their four instances (measured: 2.4 rollouts per instance and iteration on average, 48 % need more
+// than one).  Same decisions as the sequential loop of SolverFDDP::solve: a trial depends only on its own alpha.
+// One octet per instance; trial trajectory goes to slot 1 - cur.
 // ------------------------------------------------------------------------------------------------
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock) k_forward_coop(const __grid_constant__ Params P, int it) {
+__global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia) {
   const Workspace &ws = P.ws;
   const ffmpc_config &cfg = P.cfg;
   constexpr int nx = FF ? 21 : 14;
+  constexpr int cls = (NC == 0) ? 0 : 1;
+  const int nfree = ws.counts[0];
+  const int base = (NC == 0) ? 0 : nfree;
+  const int cnt = (ia == 0) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[ia * 2 + cls];
+  if ((int)(blockIdx.x * (kCoopBlock / 8)) >= cnt) return;  // whole block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
   coop_fill_table(P.mdl, P.cfg, ct);
@@ -114,19 +126,16 @@ __global__ void __launch_bounds__(kCoopBlock) k_forward_coop(const __grid_consta
   const bool act = j < NJ;
   const int lane = (int)(threadIdx.x & 31);
   const unsigned omask = 0xffu << (lane & ~7);
-  const int nfree = ws.counts[0];
-  const int base = (NC == 0) ? 0 : nfree;
-  const int cnt = (NC == 0) ? nfree : ws.counts[1];
-  if (cnt == 0) return;
+  const int *items = (ia == 0) ? (ws.perm + base) : (ws.queue + ((size_t)((ia & 1) * 2 + cls)) * ws.B);
   bool valid = o < cnt;
-  const int b = ws.perm[base + (valid ? o : 0)];
-  if (valid && ws.done[b]) valid = false;
+  const int b = items[valid ? o : 0];
+  if (valid && ia == 0 && ws.done[b]) valid = false;
   if (!__any_sync(kFull, valid)) return;
   const int cur = ws.cur[b];
   const int trial = 1 - cur;
   const bool feasible = ws.feas[b] != 0;
   double cost = ws.cost[b];
-  if (!ws.cost_valid[b]) {
+  if (ia == 0 && !ws.cost_valid[b]) {
     cost = 0.0;  // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
     for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
   }
@@ -148,96 +157,90 @@ __global__ void __launch_bounds__(kCoopBlock) k_forward_coop(const __grid_consta
   ctx.yr_v = x0[NJ + jj];
   ctx.yr_t = FF ? x0[2 * NJ + jj] : 0.0;
   const double ulim = ct[jj * CT_STRIDE + CT_TAULIM];
+  const double steplength = ldexp(1.0, -ia);
+  const bool close = feasible || (steplength == 1.0);
+  const bool wlane = valid && act;
 
-  double d1 = 0.0, d2 = 0.0, cost_try = 0.0;  // of the latest rollout that did not throw
-  double lam01[6] = {NAN, NAN, NAN, NAN, NAN, NAN};
-  int ia_ok = -1, ia_acc = -1;
-  for (int ia = 0; ia < cfg.n_alphas; ++ia) {
-    const bool has = valid && ia_acc < 0;
-    if (!__any_sync(kFull, has)) break;
-    const double steplength = ldexp(1.0, -ia);
-    const bool close = feasible || (steplength == 1.0);
-    // ---- rollout ----
-    CoopX xh;
-    xh.q = ctx.yr_q; xh.v = ctx.yr_v; xh.t = ctx.yr_t;  // x0
-    double ct_sum = 0.0, dv_part = 0.0;
-    bool failed = false;
-    for (int t = 0; t <= N; ++t) {
-      CoopX xt;
-      const double *fst = fs + (size_t)t * nx, *xst = xs + (size_t)t * nx, *vft = Vfs + (size_t)t * nx;
-      xt.q = close ? xh.q : xh.q + fst[jj] * (steplength - 1.0);
-      xt.v = close ? xh.v : xh.v + fst[NJ + jj] * (steplength - 1.0);
-      xt.t = FF ? (close ? xh.t : xh.t + fst[2 * NJ + jj] * (steplength - 1.0)) : 0.0;
-      const double dxq = xt.q - xst[jj], dxv = xt.v - xst[NJ + jj], dxt = FF ? xt.t - xst[2 * NJ + jj] : 0.0;
-      if (has && act) {
-        double *xw = xt_all + (size_t)t * nx;
-        xw[j] = xt.q;
-        xw[NJ + j] = xt.v;
-        if (FF) xw[2 * NJ + j] = xt.t;
-        dv_part += vft[j] * dxq + vft[NJ + j] * dxv + (FF ? vft[2 * NJ + j] * dxt : 0.0);  // -fs_t^T Vxx_t (xs_t - xs_try_t)
-      }
-      double u = 0.0;
-      if (t < N) {
-        // K dx: lane j multiplies its own three columns of every row, reduce-scatter gives row a to lane a
-        double pr[8];
-        const double *Kt = Kb + (size_t)t * NJ * nx;
+  // ---- rollout ----
+  CoopX xh;
+  xh.q = ctx.yr_q; xh.v = ctx.yr_v; xh.t = ctx.yr_t;  // x0
+  double ct_sum = 0.0, dv_part = 0.0;
+  bool failed = false;
+  for (int t = 0; t <= N; ++t) {
+    CoopX xt;
+    const double *fst = fs + (size_t)t * nx, *xst = xs + (size_t)t * nx, *vft = Vfs + (size_t)t * nx;
+    xt.q = close ? xh.q : xh.q + fst[jj] * (steplength - 1.0);
+    xt.v = close ? xh.v : xh.v + fst[NJ + jj] * (steplength - 1.0);
+    xt.t = FF ? (close ? xh.t : xh.t + fst[2 * NJ + jj] * (steplength - 1.0)) : 0.0;
+    const double dxq = xt.q - xst[jj], dxv = xt.v - xst[NJ + jj], dxt = FF ? xt.t - xst[2 * NJ + jj] : 0.0;
+    if (wlane) {
+      double *xw = xt_all + (size_t)t * nx;
+      xw[j] = xt.q;
+      xw[NJ + j] = xt.v;
+      if (FF) xw[2 * NJ + j] = xt.t;
+      dv_part += vft[j] * dxq + vft[NJ + j] * dxv + (FF ? vft[2 * NJ + j] * dxt : 0.0);  // -fs_t^T Vxx_t (xs_t - xs_try_t)
+    }
+    double u = 0.0;
+    if (t < N) {
+      // K dx: lane j multiplies its own three columns of every row, the reduce-scatter hands row a to lane a
+      double pr[8];
+      const double *Kt = Kb + (size_t)t * NJ * nx;
 #pragma unroll
-        for (int a = 0; a < NJ; ++a) {
-          double s = Kt[a * nx + jj] * dxq + Kt[a * nx + NJ + jj] * dxv;
-          if (FF) s += Kt[a * nx + 2 * NJ + jj] * dxt;
-          pr[a] = act ? s : 0.0;
-        }
-        pr[7] = 0.0;
-        const double kd = oct_reduce_scatter8(pr, j);
-        double s = us[t * NJ + jj] - kb[t * NJ + jj] * steplength;
-        s -= kd;
-        if (cfg.use_box_fddp) s = fmin(fmax(s, -ulim), ulim);
-        u = s;
-        if (has && act) ut_all[t * NJ + j] = s;
+      for (int a = 0; a < NJ; ++a) {
+        double s = Kt[a * nx + jj] * dxq + Kt[a * nx + NJ + jj] * dxv;
+        if (FF) s += Kt[a * nx + 2 * NJ + jj] * dxt;
+        pr[a] = act ? s : 0.0;
       }
-      ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
-      ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
-      ctx.terminal = (t == N);
-      double cst, lam[3];
-      coop_action_node<NC, FF, false>(P.mdl, cfg, ct, sm, j, ctx, xt, u, xh, cst, lam, nullptr, false);
-      if (NC != 0 && t < 2 && has && !failed) {
-        lam01[t * 3 + 0] = lam[0];
-        lam01[t * 3 + 1] = lam[1];
-        lam01[t * 3 + 2] = lam[2];
-      }
-      ct_sum += cst;
-      bool bad = false;
-      if (t < N) bad = act && !(isfinite(xh.q) && isfinite(xh.v) && isfinite(xh.t));
-      const bool anybad = (__ballot_sync(kFull, bad) & omask) != 0u;
-      if (!isfinite(ct_sum) || anybad) failed = true;  // "forward_error": this step length is skipped
+      pr[7] = 0.0;
+      const double kd = oct_reduce_scatter8(pr, j);
+      double s = us[t * NJ + jj] - kb[t * NJ + jj] * steplength;
+      s -= kd;
+      if (cfg.use_box_fddp) s = fmin(fmax(s, -ulim), ulim);
+      u = s;
+      if (wlane) ut_all[t * NJ + j] = s;
     }
-    const double dv_all = oct_sum(dv_part);  // unconditional: every lane of the warp takes part in the shuffles
-    const double dv = feasible ? 0.0 : dv_all;
-    if (has && !failed) {
-      cost_try = ct_sum;
-      ia_ok = ia;
-      const double dV = cost - ct_sum;
-      d1 = dg + dv;
-      d2 = dq - 2.0 * dv;
-      const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
-      bool acc;
-      if (dVexp >= 0.0) acc = (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp);
-      else acc = (!feasible && dV > cfg.th_acceptnegstep * dVexp);
-      if (acc) ia_acc = ia;
+    ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
+    ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
+    ctx.terminal = (t == N);
+    double cst, lam[3];
+    coop_action_node<NC, FF, false>(P.mdl, cfg, ct, sm, j, ctx, xt, u, xh, cst, lam, nullptr, false);
+    // contact forces of knots 0 / 1 as left by the last rollout that reached them (crocoddyl keeps them in the data)
+    if (NC != 0 && t < 2 && valid && j == 0 && !failed) {
+      ws.f_pred[b * 6 + t * 3 + 0] = lam[0];
+      ws.f_pred[b * 6 + t * 3 + 1] = lam[1];
+      ws.f_pred[b * 6 + t * 3 + 2] = lam[2];
     }
+    ct_sum += cst;
+    bool bad = false;
+    if (t < N) bad = act && !(isfinite(xh.q) && isfinite(xh.v) && isfinite(xh.t));
+    const bool anybad = (__ballot_sync(kFull, bad) & omask) != 0u;
+    if (!isfinite(ct_sum) || anybad) failed = true;  // "forward_error": this step length is skipped
   }
+  const double dv_all = oct_sum(dv_part);  // unconditional: every lane of the warp takes part in the shuffles
   if (!valid || j != 0) return;
-  const bool accepted = ia_acc >= 0;
-  if (NC != 0) {
-#pragma unroll
-    for (int i = 0; i < 6; ++i)
-      if (!isnan(lam01[i]) || accepted) ws.f_pred[b * 6 + i] = lam01[i];
+  const double dv = feasible ? 0.0 : dv_all;
+  bool accepted = false;
+  double d1 = ws.d1[b], d2 = ws.d2[b];  // keep the values of the last forwardPass that did not throw
+  if (!failed) {
+    const double dV = cost - ct_sum;
+    d1 = dg + dv;
+    d2 = dq - 2.0 * dv;
+    const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
+    if (dVexp >= 0.0) accepted = (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp);
+    else accepted = (!feasible && dV > cfg.th_acceptnegstep * dVexp);
   }
-  if (!accepted && ia_ok < 0) {
-    d1 = ws.d1[b];
-    d2 = ws.d2[b];
+  if (ia == 0) {
+    ws.cost_valid[b] = 1;
+    ws.cost[b] = cost;
   }
-  const double steplength = accepted ? ldexp(1.0, -ia_acc) : ldexp(1.0, -(cfg.n_alphas - 1));
+  ws.d1[b] = d1;
+  ws.d2[b] = d2;
+  if (!accepted && ia + 1 < cfg.n_alphas) {
+    // rejected: queue the instance for the next step length
+    const int pos = atomicAdd(&ws.qcount[(ia + 1) * 2 + cls], 1);
+    ws.queue[((size_t)(((ia + 1) & 1) * 2 + cls)) * ws.B + pos] = b;
+    return;
+  }
   double preg = ws.preg[b];
   int wasfeas = ws.wasfeas[b];
   if (accepted) {
@@ -245,15 +248,11 @@ __global__ void __launch_bounds__(kCoopBlock) k_forward_coop(const __grid_consta
     ws.wasfeas[b] = wasfeas;
     ws.feas[b] = (wasfeas || steplength == 1.0) ? 1 : 0;
     ws.cur[b] = trial;
-    cost = cost_try;
+    ws.cost[b] = ct_sum;
     ws.recalc[b] = 1;
   } else {
     ws.recalc[b] = 0;
   }
-  ws.cost_valid[b] = 1;
-  ws.cost[b] = cost;
-  ws.d1[b] = d1;
-  ws.d2[b] = d2;
   bool finished = false;
   int okflag = 0;
   if (steplength > cfg.th_stepdec) {

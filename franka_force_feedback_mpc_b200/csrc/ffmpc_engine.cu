@@ -161,10 +161,11 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
 #ifdef FFMPC_EMU
     if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: forward\n", it);
 #endif
-    if (h->coop) launch_forward_coop(P, it, st);
+    int nfwd = 2;
+    if (h->coop) nfwd = launch_forward_coop(P, it, st);
     else launch_forward(P, it, std::min(h->lgA_max, fwd_lanes_log2(B, h->cfg.n_alphas)), st);
-    if (int e = mark(h, FFMPC_FAM_FORWARD, 2)) return e;
-    launches += 5;
+    if (int e = mark(h, FFMPC_FAM_FORWARD, nfwd)) return e;
+    launches += 3 + nfwd;
   }
   CU(cudaGetLastError());
   return FFMPC_OK;
@@ -299,6 +300,8 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   DA(ws.feas, B); DA(ws.wasfeas, B); DA(ws.recalc, B); DA(ws.done, B); DA(ws.ok, B); DA(ws.iter, B); DA(ws.cur, B);
   DA(ws.cost_valid, B);
   DA(ws.f_pred, B * 6);
+  DA(ws.queue, 4 * B);
+  DA(ws.qcount, 64);
 #undef DA
   if (rc != FFMPC_OK) {
     ffmpc_destroy(h);

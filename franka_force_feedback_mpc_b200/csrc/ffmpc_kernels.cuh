@@ -36,6 +36,8 @@ struct Workspace {
   double *preg, *cost, *dg, *dq, *stop, *d1, *d2;
   int *feas, *wasfeas, *recalc, *done, *ok, *iter, *cur, *cost_valid;
   double *f_pred;   // [B,2,3]
+  int *queue;       // [2 parity][2 mode buckets][B] instances still in the line search (k_forward_coop)
+  int *qcount;      // [32][2] number of queued instances per step-length pass and mode bucket
 };
 
 struct Params {

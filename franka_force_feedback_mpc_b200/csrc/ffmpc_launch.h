@@ -33,5 +33,5 @@ int prepare_coop_node();
 int prepare_coop_fwd();
 void launch_node_diff_coop(const Params &P, cudaStream_t st);
 void launch_node_eval_coop(const Params &P, const NodeEvalArgs &A, double *rec, cudaStream_t st);
-void launch_forward_coop(const Params &P, int it, cudaStream_t st);
+int launch_forward_coop(const Params &P, int it, cudaStream_t st);  // returns the number of kernel launches
 }  // namespace ffmpc

@@ -15,7 +15,7 @@ from . import _abi
 from .batch import (BatchInputs, OUTPUT_NAMES, alloc_node_outputs, alloc_outputs, node_outputs_abi, outputs_abi, ptr)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libffmpc_b200.so")
+LIB_PATH = os.environ.get("FFMPC_LIB") or os.path.join(_HERE, "csrc", "libffmpc_b200.so")  # FFMPC_LIB: A/B builds of the same engine
 _lib = None
 
 

@@ -48,6 +48,10 @@ constexpr int NZ = 21;  // (q, v, u) stacking of the inner DAM
 // ----------------------------------------------------------------------------------------------
 // forward-mode scalar
 // ----------------------------------------------------------------------------------------------
+// work counters (how many rollouts the line search really runs): feeds the FLOP accounting of bench.py / DESIGN.md
+std::atomic<long long> g_rollouts{0}, g_iterations{0};
+std::atomic<long long> g_trial_hist[32];
+
 struct Dual {
   double v;
   double d[NZ];
@@ -1137,8 +1141,11 @@ struct Solver {
       update_expected_improvement();
       recalc = false;
       steplength = 1.0;
+      g_iterations.fetch_add(1, std::memory_order_relaxed);
       for (int ia = 0; ia < c.n_alphas; ++ia) {
         steplength = std::ldexp(1.0, -ia);
+        g_rollouts.fetch_add(1, std::memory_order_relaxed);
+        g_trial_hist[ia].fetch_add(1, std::memory_order_relaxed);
         if (!forward_pass(steplength)) continue;
         dV = cost - cost_try;
         expected_improvement();
@@ -1381,3 +1388,15 @@ void ffmpc_oracle_frame_jacobian(const ffmpc_model *mdl, const double *q, double
 }
 
 }  // extern "C"
+
+extern "C" void ffmpc_oracle_rollout_stats(long long *rollouts, long long *iterations, long long *trial_hist32, int reset) {
+  if (rollouts) *rollouts = g_rollouts.load();
+  if (iterations) *iterations = g_iterations.load();
+  if (trial_hist32)
+    for (int i = 0; i < 32; ++i) trial_hist32[i] = g_trial_hist[i].load();
+  if (reset) {
+    g_rollouts = 0;
+    g_iterations = 0;
+    for (int i = 0; i < 32; ++i) g_trial_hist[i] = 0;
+  }
+}
