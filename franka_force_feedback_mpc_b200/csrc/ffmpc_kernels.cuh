@@ -413,7 +413,9 @@ template <bool FF> struct BwdLayout {
   static constexpr int oVX = oSS + 56;
   static constexpr int oFS = oVX + 24;
   static constexpr int oDI = oFS + 24;   // reciprocal pivots
-  static constexpr int TOTAL = oDI + 8;  // doubles per warp (even: every warp region stays 16-byte aligned)
+  static constexpr int oTT = oDI + 8;    // Tt rows (Pt^T V Et), operand of the blocked Qxx assembly
+  static constexpr int oKT = oTT + n * RS;  // K^T rows (K[:, c]), operand of the blocked Vxx update
+  static constexpr int TOTAL = oKT + n * RS;  // doubles per warp (even: every warp region stays 16-byte aligned)
   static_assert(n * RS >= 56 && TOTAL % 2 == 0 && oVE % 2 == 0, "layout");
 };
 
@@ -466,7 +468,22 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
   const bool box = cfg.use_box_fddp && feasible;
   double *REC = sm + LYT::oREC, *V = sm + LYT::oV, *VEs = sm + LYT::oVE, *YS = sm + LYT::oYS, *GT = sm + LYT::oGT,
          *QXU = sm + LYT::oQXU, *SS = sm + LYT::oSS, *LL = sm + LYT::oLL, *HI = sm + LYT::oHI, *VX = sm + LYT::oVX,
-         *FS = sm + LYT::oFS, *DI = sm + LYT::oDI;
+         *FS = sm + LYT::oFS, *DI = sm + LYT::oDI, *TT = sm + LYT::oTT, *KT = sm + LYT::oKT;
+  // 3x3 register blocks of the symmetric nx x nx matrices (Qxx, Vxx): lane l < NBLK owns block (bI, bJ), bI <= bJ, of the
+  // upper triangle.  Every operand row loaded from shared memory then feeds three FMAs (the column-per-lane form fed one and
+  // was bound by the shared-memory return path), and only the upper triangle is computed.
+  constexpr int NB = n / 3;                 // 7 (FF) -- classical n = 14 is padded: see NB3 below
+  constexpr int NB3 = (n + 2) / 3;          // block rows: 7 (n = 21), 5 (n = 14, last block is 2 wide)
+  constexpr int NBLK = NB3 * (NB3 + 1) / 2; // 28 / 15
+  (void)NB;
+  int bI = 0, bJ = 0;
+  {
+    int idx = lane < NBLK ? lane : NBLK - 1, len = NB3;
+    while (idx >= len) { idx -= len; ++bI; --len; }
+    bJ = bI + idx;
+  }
+  const bool blk = lane < NBLK;
+  const int i0 = 3 * bI, c0 = 3 * bJ;
   const double *recb = ws.rec + (size_t)b * (N + 1) * REC_SIZE;
   const double *fsb = ws.fs + (size_t)b * (N + 1) * n;
   const double *usb = ws.us + ((size_t)ws.cur[b] * ws.B + b) * N * NJ;
@@ -543,7 +560,10 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int k = 0; k < NJ; ++k)
 #pragma unroll
         for (int l = 0; l < NJ; ++l) y[l] += g[k] * SS[k * 8 + l];
-      if (act) st7(YS + c * RS, y);
+      if (act) {
+        st7(YS + c * RS, y);
+        st7(TT + c * RS, tt);
+      }
       // (g) Qxu row c (classical: Lxu + Y Gu)
       if (!FF) {
 #pragma unroll
@@ -604,27 +624,55 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int k = 0; k < NJ; ++k) qu += (dt * G[k * NZ + 2 * NJ + r7]) * (dt * VX[k] + VX[NJ + k]);
     }
     __syncwarp();  // YS / GT / QXU visible to every lane
-    // (e) Qxx column c
-    double qxx[n];
+    // (e) Qxx = Pt^T V Pt + Lxx + Y Gh + Gh^T Tt^T, upper-triangular 3x3 block (bI, bJ) per lane
+    double qb[3][3];
+    {
+      // Pt^T V Pt: column / row c of Pt picks V[c] (x alpha for the torque block) plus dt V[c-7] on the velocity block
 #pragma unroll
-    for (int i = 0; i < n; ++i) {
-      double wi = V[i * LD + c];
-      if (c >= NJ && c < 2 * NJ) wi += dt * V[i * LD + c - NJ];
-      if (FF && c >= 2 * NJ) wi *= alpha;
-      qxx[i] = wi;
-    }
+      for (int r = 0; r < 3; ++r) {
+        const int i = (i0 + r < n) ? i0 + r : n - 1;
+        const bool imid = (i >= NJ && i < 2 * NJ);
+        const double si = (FF && i >= 2 * NJ) ? alpha : 1.0;
 #pragma unroll
-    for (int i = n - 1; i >= 0; --i) {
-      double acc = qxx[i];
-      if (i >= NJ && i < 2 * NJ) acc += dt * qxx[i - NJ];
-      if (FF && i >= 2 * NJ) acc *= alpha;
-      acc += LZZ_AT(i);
-      double yr[NJ], gr[NJ];
-      ld7(YS + i * RS, yr);
-      ld7(GT + i * RS, gr);
+        for (int s2 = 0; s2 < 3; ++s2) {
+          const int cc = (c0 + s2 < n) ? c0 + s2 : n - 1;
+          const bool cmid = (cc >= NJ && cc < 2 * NJ);
+          const double sc2 = (FF && cc >= 2 * NJ) ? alpha : 1.0;
+          double w = V[i * LD + cc];
+          if (cmid) w += dt * V[i * LD + cc - NJ];
+          if (imid) {
+            double w2 = V[(i - NJ) * LD + cc];
+            if (cmid) w2 += dt * V[(i - NJ) * LD + cc - NJ];
+            w += dt * w2;
+          }
+          const int lo = i < cc ? i : cc, hi = i < cc ? cc : i;
+          qb[r][s2] = si * sc2 * w + REC[REC_LZZ + lo * NZ - (lo * (lo - 1)) / 2 + (hi - lo)];
+        }
+      }
+      const int ir[3] = {i0, (i0 + 1 < n) ? i0 + 1 : n - 1, (i0 + 2 < n) ? i0 + 2 : n - 1};
+      const int cr[3] = {c0, (c0 + 1 < n) ? c0 + 1 : n - 1, (c0 + 2 < n) ? c0 + 2 : n - 1};
 #pragma unroll
-      for (int k = 0; k < NJ; ++k) acc += yr[k] * g[k] + gr[k] * tt[k];
-      qxx[i] = acc;
+      for (int k = 0; k < 8; k += 2) {
+        double yI[3][2], gI[3][2], gJ[3][2], tJ[3][2];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const dbl2 a1 = *reinterpret_cast<const dbl2 *>(YS + ir[r] * RS + k);
+          const dbl2 a2 = *reinterpret_cast<const dbl2 *>(GT + ir[r] * RS + k);
+          const dbl2 a3 = *reinterpret_cast<const dbl2 *>(GT + cr[r] * RS + k);
+          const dbl2 a4 = *reinterpret_cast<const dbl2 *>(TT + cr[r] * RS + k);
+          yI[r][0] = a1.x; yI[r][1] = a1.y;
+          gI[r][0] = a2.x; gI[r][1] = a2.y;
+          gJ[r][0] = a3.x; gJ[r][1] = a3.y;
+          tJ[r][0] = a4.x; tJ[r][1] = a4.y;
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s2 = 0; s2 < 3; ++s2) {
+            qb[r][s2] += yI[r][0] * gJ[s2][0] + gI[r][0] * tJ[s2][0];
+            if (k + 1 < NJ) qb[r][s2] += yI[r][1] * gJ[s2][1] + gI[r][1] * tJ[s2][1];
+          }
+      }
     }
     __syncwarp();  // every lane is done with this knot's record
     if (t > 0) rec_prefetch(REC, recb + (size_t)(t - 1) * REC_SIZE, lane);
@@ -684,9 +732,9 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int a = 0; a < NJ; ++a) kc[a] = 0.0;
 #pragma unroll
       for (int bb = 0; bb < NJ; ++bb) {
-        const double qb = QXU[c * RS + bb];
+        const double qxb = QXU[c * RS + bb];
 #pragma unroll
-        for (int a = 0; a < NJ; ++a) kc[a] += HI[a * 8 + bb] * qb;
+        for (int a = 0; a < NJ; ++a) kc[a] += HI[a * 8 + bb] * qxb;
       }
       gather7(kv, kvv);
     }
@@ -694,6 +742,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     if (act) {
 #pragma unroll
       for (int a = 0; a < NJ; ++a) Kb[((size_t)t * NJ + a) * n + c] = kc[a];
+      st7(KT + c * RS, kc);
     }
     // value function: wv = Quu k - 2 Qu (row r7), dg += Qu.k, dq -= k.Quu k
     double wv[NJ];
@@ -706,41 +755,58 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     double vx = qx;
 #pragma unroll
     for (int a = 0; a < NJ; ++a) vx += kc[a] * wv[a];
-    // Vxx = Qxx - Qxu K, column c
+    // Vxx = Qxx - Qxu K (+ preg), symmetric: upper 3x3 block per lane, mirrored into shared memory
+    __syncwarp();  // KT visible; every reader of the old V is done
+    bool bad = false;
+    {
+      const int ir[3] = {i0, (i0 + 1 < n) ? i0 + 1 : n - 1, (i0 + 2 < n) ? i0 + 2 : n - 1};
+      const int cr[3] = {c0, (c0 + 1 < n) ? c0 + 1 : n - 1, (c0 + 2 < n) ? c0 + 2 : n - 1};
 #pragma unroll
-    for (int i = 0; i < n; ++i) {
-      double s = qxx[i];
-      double qr[NJ];
-      ld7(QXU + i * RS, qr);
+      for (int k = 0; k < 8; k += 2) {
+        double qI[3][2], kJ[3][2];
 #pragma unroll
-      for (int a = 0; a < NJ; ++a) s -= qr[a] * kc[a];
-      qxx[i] = s;
-      if (act) V[i * LD + c] = s;
+        for (int r = 0; r < 3; ++r) {
+          const dbl2 a1 = *reinterpret_cast<const dbl2 *>(QXU + ir[r] * RS + k);
+          const dbl2 a2 = *reinterpret_cast<const dbl2 *>(KT + cr[r] * RS + k);
+          qI[r][0] = a1.x; qI[r][1] = a1.y;
+          kJ[r][0] = a2.x; kJ[r][1] = a2.y;
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s2 = 0; s2 < 3; ++s2) {
+            qb[r][s2] -= qI[r][0] * kJ[s2][0];
+            if (k + 1 < NJ) qb[r][s2] -= qI[r][1] * kJ[s2][1];
+          }
+      }
+      if (blk) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s2 = 0; s2 < 3; ++s2) {
+            const int i = i0 + r, cc = c0 + s2;
+            if (i < n && cc < n && i <= cc) {
+              const double v = qb[r][s2] + ((i == cc) ? preg : 0.0);
+              bad = bad || !isfinite(v);
+              V[i * LD + cc] = v;
+              V[cc * LD + i] = v;
+            }
+          }
+      }
     }
     __syncwarp();
-    bool bad = false;
     double vf = 0.0;
 #pragma unroll
-    for (int i = 0; i < n; ++i) {
-      const double s = 0.5 * (qxx[i] + V[c * LD + i]) + ((i == c) ? preg : 0.0);
-      qxx[i] = s;
-      vf += s * FS[i];
-      bad = bad || !isfinite(s);
-    }
-    __syncwarp();
-    if (act) {
-#pragma unroll
-      for (int i = 0; i < n; ++i) V[i * LD + c] = qxx[i];
-      Vfsb[t * n + lane] = vf;
-    }
+    for (int i = 0; i < n; ++i) vf += V[i * LD + c] * FS[i];
+    if (act) Vfsb[t * n + lane] = vf;
     if (!feasible) vx += vf;
-    bad = bad || !isfinite(vx);
+    bad = bad || (act && !isfinite(vx));
     if (act) VX[lane] = vx;
     if (!feasible) {
       dg -= warp_sum(act ? vx * FS[c] : 0.0);
       dq += warp_sum(act ? vf * FS[c] : 0.0);
     }
-    if (__any_sync(0xffffffffu, bad && act)) {
+    if (__any_sync(0xffffffffu, bad)) {
       rec_wait();
       return false;
     }
@@ -754,7 +820,7 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
 }
 
 template <bool FF>
-__global__ void __launch_bounds__(128, 4) k_backward(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(128, 3) k_backward(const __grid_constant__ Params P) {
 #ifdef FFMPC_EMU
   double *smem = (double *)emu::S().smem;
 #else
