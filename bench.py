@@ -8,9 +8,9 @@
 Workload (BASELINE.json config 4, the configuration the 1e5 solves/s/GPU target is quoted on):
 ForceFeedbackCrocoddylMPC OCP (nx=21, nu=7), normal_1d contact, horizon 50, dt_ocp 0.01, Box-FDDP with
 a FIXED 10 iterations (converged early exit disabled), cold start, synthetic x0 / reference
-trajectories: every GPU solves `--batch` (default 16384) instances made of the four sweep scenarios
-tilted_5 / tilted_10 / tilted_15 / actuation_uncertainty in equal parts (16384 x 4 GPUs = the 65536 of
-config 4).  One step = one batched solve of the whole per-GPU batch.  Instances are independent:
+trajectories: every GPU solves `--batch` instances (default 65536 = the whole of config 4, which fits one
+GPU: 4 scenarios x 16384) made of the four sweep scenarios tilted_5 / tilted_10 / tilted_15 /
+actuation_uncertainty in equal parts.  One step = one batched solve of the whole per-GPU batch.  Instances are independent:
 ranks shard them, there is no collective on the solve path (weak scaling).
 
 Printed JSON line (rank 0): see the keys below; `value` = device-resident throughput (CUDA events on
@@ -71,7 +71,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=16384, help="instances per GPU per step")
+    ap.add_argument("--batch", type=int, default=65536, help="instances per GPU per step (default: all of BASELINE config 4)")
     ap.add_argument("--horizon", type=int, default=50)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--variant", default="ff", choices=["ff", "classical"])
@@ -80,7 +80,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.n_alphas_report = 10
+    return a
 
 
 def make_problem(args, rank: int, B: int):
@@ -181,10 +183,13 @@ def cpu_baseline(args, cfg, model, inp, nthreads: int) -> dict:
     lib, how = orc.timing_lib()
     rate = _cpu_rate_probe(args, cfg, model, inp, lib, nthreads)
     sub = inp.slice(np.arange(_cpu_sample_size(args, rate, 15.0, inp.B, nthreads)))
+    orc.rollout_stats(reset=True, _use=lib)
     t0 = time.perf_counter()
     orc.solve_batch(cfg, model, sub, args.iters, True, nthreads=nthreads, _use=lib)
     dt = time.perf_counter() - t0
+    nroll, niter, hist = orc.rollout_stats(_use=lib)
     return {"value": sub.B / dt, "unit": UNIT, "cores": nthreads, "kind": "port",
+            "rollouts_per_iteration": (nroll / niter) if niter else None, "trials_per_step_length": hist[:args.n_alphas_report],
             "sample": f"first {sub.B} instances of the same batch, {args.iters} fixed iterations, oracle/ffmpc_oracle.cpp ({how}), "
                       f"{nthreads} threads over instances, {dt:.1f} s",
             "note": "reference's own CPU path (Crocoddyl/Pinocchio via Python) is not installable on this box"}
@@ -345,7 +350,13 @@ def main():
             dist.destroy_process_group()
         return
 
-    # ---- rank 0 only: roofline, latency, CPU baseline ----
+    # ---- rank 0 only: CPU baseline (also counts the rollouts the line search really runs), roofline, latency ----
+    cpu = None
+    rollouts = 1.0
+    if not args.no_cpu_baseline:
+        nthreads = os.cpu_count() or 1
+        cpu = cpu_baseline(args, cfg, model, inp, nthreads)
+        rollouts = cpu.get("rollouts_per_iteration") or 1.0
     value = world * B * args.steps / (ms_total * 1e-3)
     e2e_val = world * B * args.steps / e2e_s
     peak_tf = engine.dfma_peak_tflops(local_rank)
@@ -353,7 +364,7 @@ def main():
     fam_flop = {
         "node_diff": knots * F_DIFF[nc] * args.iters,
         "backward": B * N * f_bwd(nx) * args.iters,
-        "forward": knots * (F_CALC[nc] + F_EI[nx]) * args.iters,  # >= one rollout per iteration
+        "forward": knots * (rollouts * F_CALC[nc] + F_EI[nx]) * args.iters,  # rollouts per iteration as counted by the CPU port
     }
     dom = max(("node_diff", "backward", "forward"), key=lambda n: fam_ms[n])
     dom_launches = max(1, fam_launch[dom])
@@ -375,9 +386,9 @@ def main():
         "kernel_ms_per_step": {n: fam_ms[n] for n in _abi.FAMILY_NAMES},
         "kernel_share": {n: (fam_ms[n] / solve_ms if solve_ms else None) for n in _abi.FAMILY_NAMES},
         "whole_solve": {
-            "flop_per_solve": flop_per_solve(nx, nc, N, args.iters),
-            "achieved_tflops": value / world * flop_per_solve(nx, nc, N, args.iters) * 1e-12,
-            "frac_of_fp64_peak": value / world * flop_per_solve(nx, nc, N, args.iters) * 1e-12 / peak_tf if peak_tf else None,
+            "flop_per_solve": flop_per_solve(nx, nc, N, args.iters, rollouts), "rollouts_per_iteration": rollouts,
+            "achieved_tflops": value / world * flop_per_solve(nx, nc, N, args.iters, rollouts) * 1e-12,
+            "frac_of_fp64_peak": value / world * flop_per_solve(nx, nc, N, args.iters, rollouts) * 1e-12 / peak_tf if peak_tf else None,
             "io_bytes_per_solve": io_bytes_per_solve(nx, N),
             "hbm_gbs_compulsory": value / world * io_bytes_per_solve(nx, N) * 1e-9,
             "hbm_peak_gbs": hbm_peak, "hbm_peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
@@ -399,11 +410,6 @@ def main():
         latency = {"p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)), "n": int(lat.size),
                    "what": "B=1 solve through ffmpc_solve_batch_host (H2D + 10 fixed iterations + D2H), wall clock"}
         eng1.close()
-
-    cpu = None
-    if not args.no_cpu_baseline:
-        nthreads = os.cpu_count() or 1
-        cpu = cpu_baseline(args, cfg, model, inp, nthreads)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

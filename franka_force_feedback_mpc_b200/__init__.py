@@ -10,9 +10,12 @@ from .config import (  # noqa: F401
     benchmark_classical_config,
     benchmark_ff_config,
 )
+from .controllers import ClassicalCrocoddylMPC, ForceFeedbackCrocoddylMPC  # noqa: F401
 from .panda import PandaModel, default_model  # noqa: F401
 
 __all__ = [
+    "ClassicalCrocoddylMPC",
+    "ForceFeedbackCrocoddylMPC",
     "ClassicalMPCConfig",
     "ForceFeedbackMPCConfig",
     "benchmark_classical_config",

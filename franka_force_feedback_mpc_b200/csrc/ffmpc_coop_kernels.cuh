@@ -15,6 +15,10 @@ constexpr int kCoopBlock = 128;
 #define FFMPC_COOP_MINBLOCKS 3  // resident blocks per SM the register allocation is sized for
 #endif
 constexpr size_t kCoopSmemBytes = (size_t)(CT_SIZE + (kCoopBlock / 8) * CS_SIZE) * sizeof(double);
+// the rollout is latency-bound (51 dependent knots per instance): one warp (4 instances) per block spreads a small
+// line-search queue over all SMs instead of packing it into a few 4-warp blocks
+constexpr int kFwdCoopBlock = 32;
+constexpr size_t kFwdCoopSmemBytes = (size_t)(CT_SIZE + (kFwdCoopBlock / 8) * CS_SIZE) * sizeof(double);
 
 FFMPC_DEV double *coop_smem_base() {
 #ifdef FFMPC_EMU
@@ -114,7 +118,7 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
   const int nfree = ws.counts[0];
   const int base = (NC == 0) ? 0 : nfree;
   const int cnt = (ia == 0) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[ia * 2 + cls];
-  if ((int)(blockIdx.x * (kCoopBlock / 8)) >= cnt) return;  // whole block without work (block-uniform)
+  if ((int)(blockIdx.x * (blockDim.x >> 3)) >= cnt) return;  // whole block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
   coop_fill_table(P.mdl, P.cfg, ct);

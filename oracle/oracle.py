@@ -144,3 +144,15 @@ def frame_jacobian(model: _abi.Model, q):
     J = np.zeros((6, 7))
     lib().ffmpc_oracle_frame_jacobian(C.byref(model), _ptr(q), _ptr(J))
     return J
+
+
+def rollout_stats(reset: bool = False, _use=None):
+    """(rollouts, iterations, per-step-length trial histogram) counted by the oracle's line search since the last reset:
+    how many forward passes the FDDP iterations really ran (feeds the FLOP accounting of bench.py)."""
+    L = _use if _use is not None else lib()
+    r, i = C.c_longlong(), C.c_longlong()
+    h = (C.c_longlong * 32)()
+    L.ffmpc_oracle_rollout_stats.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    L.ffmpc_oracle_rollout_stats.restype = None
+    L.ffmpc_oracle_rollout_stats(C.byref(r), C.byref(i), h, int(bool(reset)))
+    return r.value, i.value, list(h)

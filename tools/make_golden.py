@@ -164,6 +164,101 @@ def gen_misc():
     print("misc_golden.npz", len(rows))
 
 
+def gen_ctrl():
+    """Host-side per-tick logic of the two controller classes, executed from the reference source on bare instances
+    (object.__new__: the constructors need pinocchio / example_robot_data) -> ctrl_golden.npz."""
+    from src.mpc.crocoddyl_classical import ClassicalCrocoddylMPC as RC, ClassicalMPCConfig as RCC
+    from src.mpc.crocoddyl_force_feedback import ForceFeedbackCrocoddylMPC as RF, ForceFeedbackMPCConfig as RFC
+
+    rng = np.random.default_rng(2024)
+    out = {}
+    N = 6
+
+    def bare(cls, cfg, dt=0.005):
+        o = object.__new__(cls)
+        o.cfg = cfg
+        o.sim = types.SimpleNamespace(dt=dt)
+        o._warned_keys = set()
+        o._tau_prev = rng.normal(0, 2.0, 7)
+        o.actuation = types.SimpleNamespace(nu=7)
+        o.nx_mb, o.ndx_mb, o.nx_aug = 14, 14, 21
+        o.xs = o.us = o.Ks = o.ks = None
+        o._surface_latched, o._contact_loss_count = False, 0
+        return o
+
+    # ---- policy + shift, classical ----
+    c = bare(RC, RCC(horizon=N, feedback_gain_scale=0.7))
+    out["c_tau_prev"] = c._tau_prev.copy()
+    x_now = rng.normal(0, 1, 14)
+    out["c_x_now"] = x_now
+    out["c_policy_cold"] = c._policy_control(x_now)[0]
+    xs0, us0 = c._shift_guess(x_now, N)
+    out["c_shift_cold_xs"], out["c_shift_cold_us"] = np.stack(xs0), np.stack(us0)
+    for tag, L in (("full", N), ("short", N - 2), ("long", N + 3)):
+        c.xs = [rng.normal(0, 1, 14) for _ in range(L + 1)]
+        c.us = [rng.normal(0, 5, 7) for _ in range(L)]
+        c.Ks = [rng.normal(0, 3, (7, 14)) for _ in range(L)]
+        out[f"c_{tag}_xs"], out[f"c_{tag}_us"], out[f"c_{tag}_Ks"] = np.stack(c.xs), np.stack(c.us), np.stack(c.Ks)
+        out[f"c_{tag}_policy"] = c._policy_control(x_now)[0]
+        xs1, us1 = c._shift_guess(x_now, N)
+        out[f"c_{tag}_shift_xs"], out[f"c_{tag}_shift_us"] = np.stack(xs1), np.stack(us1)
+
+    # ---- command filter ----
+    for tag, filt in (("raw", False), ("filt", True)):
+        c = bare(RC, RCC(apply_command_filter=filt))
+        out[f"safe_{tag}_prev0"] = c._tau_prev.copy()
+        targets = rng.normal(0, 60.0, (12, 7))
+        targets[3, 2] = np.nan
+        targets[7] *= 5.0
+        out[f"safe_{tag}_in"] = targets
+        out[f"safe_{tag}_out"] = np.stack([c._safe_tau(tg) for tg in targets])
+
+    # ---- surface latch ----
+    c = bare(RC, RCC(phase_source="force_latch", contact_release_steps=4))
+    fn = np.concatenate([np.zeros(5), [0.2, 2.5, 3.0, 0.1, 0.1, 0.1, 6.0, 0.1, 0.1, 0.1, 0.1, 0.1, 0.0], np.zeros(4), [0.0, 0.0]])
+    ez = np.concatenate([np.full(5, 0.40), np.full(13, 0.352), np.full(4, 0.45), [0.355, 0.45]])
+    hint = np.concatenate([np.zeros(3, bool), np.ones(fn.size - 3, bool)])
+    hint[-5:-2] = False
+    res = []
+    for a, b, h in zip(fn, ez, hint):
+        obs = types.SimpleNamespace(f_contact_normal=float(a), ee_pos=np.array([0.0, 0.0, float(b)]))
+        res.append(c._detect_surface(obs, 0.0, bool(h)))
+    out["latch_fn"], out["latch_ez"], out["latch_hint"], out["latch_out"] = fn, ez, hint, np.array(res)
+
+    # ---- FF policy (Eq. 14-18), tau state source, force-prediction alignment ----
+    for tag, interp, dt in (("interp", True, 0.005), ("nointerp", False, 0.005), ("fullstep", True, 0.01)):
+        f = bare(RF, RFC(horizon=N, ff_use_tau_interpolation=interp, ff_cutoff_hz=25.0, dt_ocp=0.01), dt=dt)
+        f.__class__._dt_ocp.fget  # property exists on the reference class
+        y_now = rng.normal(0, 1, 21)
+        out[f"f_{tag}_y_now"] = y_now
+        out[f"f_{tag}_cold"] = f._policy_control(y_now)[0]
+        f.xs = [rng.normal(0, 1, 21) for _ in range(N + 1)]
+        f.us = [rng.normal(0, 5, 7) for _ in range(N)]
+        f.Ks = [rng.normal(0, 3, (7, 21)) for _ in range(N)]
+        out[f"f_{tag}_xs"], out[f"f_{tag}_us"], out[f"f_{tag}_Ks"] = np.stack(f.xs), np.stack(f.us), np.stack(f.Ks)
+        out[f"f_{tag}_policy"] = f._policy_control(y_now)[0]
+        xs1, us1 = f._shift_guess(y_now, N)
+        out[f"f_{tag}_shift_xs"], out[f"f_{tag}_shift_us"] = np.stack(xs1), np.stack(us1)
+        f.xs = f.us = None
+        xs1, us1 = f._shift_guess(y_now, N)
+        out[f"f_{tag}_shift_cold_us"] = np.stack(us1)
+    f = bare(RF, RFC(ff_align_min_samples=20, ff_align_window=64, ff_align_max_lag=4))
+    f._fn_pred_corr, f._fn_pred_hist_raw, f._fn_pred_hist_meas = np.nan, [], []
+    T = 90
+    raw = 8.0 + 2.0 * np.sin(np.arange(T) * 0.2) + rng.normal(0, 0.1, T)
+    meas = 1.1 * np.roll(raw, 2) + 0.5 + rng.normal(0, 0.1, T)
+    meas[10] = np.nan
+    surf = np.ones(T, bool)
+    surf[:3] = False
+    res, corr = [], []
+    for a, b, sfc in zip(raw, meas, surf):
+        res.append(f._align_logged_force_prediction(float(a), float(b), bool(sfc)))
+        corr.append(f._fn_pred_corr)
+    out["align_raw"], out["align_meas"], out["align_surf"], out["align_out"], out["align_corr"] = raw, meas, surf, np.array(res), np.array(corr)
+    np.savez_compressed(os.path.join(GOLD, "ctrl_golden.npz"), **out)
+    print("ctrl_golden.npz", len(out), "arrays")
+
+
 def main():
     if not os.path.isdir(REF):
         raise SystemExit(f"{REF} not found: the golden fixtures can only be regenerated where the reference is mounted")
@@ -173,6 +268,7 @@ def main():
     gen_lpf()
     gen_traj()
     gen_misc()
+    gen_ctrl()
 
 
 if __name__ == "__main__":
