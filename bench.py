@@ -382,7 +382,11 @@ def main():
         "kernel": dom, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
         "peak_source": "fp64 DFMA micro-benchmark run by this bench (ffmpc_dfma_peak); MEASURED_PEAKS.json has no fp64 entry",
         "flop_per_launch": fam_flop[dom] / dom_launches, "ms_per_launch": fam_ms[dom] / dom_launches,
-        "traffic": None,
+        # DRAM bytes of the dominant kernel per launch: per-knot figure from the ncu --set full capture committed under
+        # profiles/ (r1d, B=4096: backward 754 MB read + 283 MB written for 204800 knot steps; node_diff 65 MB + 1062 MB for
+        # 208896 knots), scaled to this launch's knots -- about equal to the algorithmic bytes (record 3328 B + gains 1232 B
+        # + gaps / Vxx fs 336 B per knot): no wasted re-reads
+        "traffic": {"backward": 5063.0 * B * N, "node_diff": 5395.0 * knots}.get(dom),
         "kernel_ms_per_step": {n: fam_ms[n] for n in _abi.FAMILY_NAMES},
         "kernel_share": {n: (fam_ms[n] / solve_ms if solve_ms else None) for n in _abi.FAMILY_NAMES},
         "whole_solve": {
