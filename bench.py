@@ -350,6 +350,33 @@ def main():
             dist.destroy_process_group()
         return
 
+    # B=1 latency first: it is launch-bound wall clock, measure it before the CPU baseline loads every host core
+    latency = None
+    if not args.no_latency:
+        one = inp.slice(np.arange(1))
+        eng1 = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=1)
+        o1 = None
+        lat = []
+        for i in range(60):
+            t0 = time.perf_counter()
+            o1 = eng1.solve_host(one, args.iters, True, want=("xs", "us", "K", "cost", "iters", "ok"), out=o1)
+            lat.append(time.perf_counter() - t0)
+        lat = np.array(lat[10:]) * 1e3
+        latency = {"p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)), "n": int(lat.size),
+                   "what": "B=1 solve through ffmpc_solve_batch_host (H2D + 10 fixed iterations + D2H), wall clock"}
+        eng1.close()
+        if not args.no_cpu_baseline:
+            # the same single instance on ONE host core (B=1 GPU latency vs the CPU port on 1 core)
+            from oracle import oracle as orc
+
+            lib, how = orc.timing_lib()
+            cl = []
+            for i in range(7):
+                t0 = time.perf_counter()
+                orc.solve_batch(cfg, model, one, args.iters, True, nthreads=1, _use=lib)
+                cl.append(time.perf_counter() - t0)
+            latency["cpu_port_1core_p50_ms"] = float(np.percentile(np.array(cl[2:]) * 1e3, 50))
+
     # ---- rank 0 only: CPU baseline (also counts the rollouts the line search really runs), roofline, latency ----
     cpu = None
     rollouts = 1.0
@@ -399,21 +426,6 @@ def main():
             "frac_of_hbm_peak": value / world * io_bytes_per_solve(nx, N) * 1e-9 / hbm_peak,
         },
     }
-
-    latency = None
-    if not args.no_latency:
-        one = inp.slice(np.arange(1))
-        eng1 = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=1)
-        o1 = None
-        lat = []
-        for i in range(60):
-            t0 = time.perf_counter()
-            o1 = eng1.solve_host(one, args.iters, True, want=("xs", "us", "K", "cost", "iters", "ok"), out=o1)
-            lat.append(time.perf_counter() - t0)
-        lat = np.array(lat[10:]) * 1e3
-        latency = {"p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)), "n": int(lat.size),
-                   "what": "B=1 solve through ffmpc_solve_batch_host (H2D + 10 fixed iterations + D2H), wall clock"}
-        eng1.close()
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -20,6 +20,16 @@ constexpr size_t kCoopSmemBytes = (size_t)(CT_SIZE + (kCoopBlock / 8) * CS_SIZE)
 constexpr int kFwdCoopBlock = 32;
 constexpr size_t kFwdCoopSmemBytes = (size_t)(CT_SIZE + (kFwdCoopBlock / 8) * CS_SIZE) * sizeof(double);
 
+// bring one 128-byte line into L1 ahead of use (no register cost); the rollout issues these for knot t+1 while knot t
+// is evaluated: its global operands (K_t, xs_t, fs_t, Vxx fs_t, us_t, k_t, references) do not depend on the rollout state
+FFMPC_DEV void prefetch_l1(const void *p) {
+#if !defined(FFMPC_EMU)
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+  (void)p;
+#endif
+}
+
 FFMPC_DEV double *coop_smem_base() {
 #ifdef FFMPC_EMU
   return (double *)emu::S().smem;
@@ -206,6 +216,22 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
     ctx.p_ref = ws.p_ref + ((size_t)b * (N + 1) + t) * 3;
     ctx.v_ref = ws.v_ref + ((size_t)b * (N + 1) + t) * 3;
     ctx.terminal = (t == N);
+    if (t < N) {
+      // next knot's operands -> L1 (lines spread over the 8 lanes of the octet)
+      const char *Kn = (const char *)(Kb + (size_t)(t + 1) * NJ * nx);
+      if (t + 1 < N) {
+        prefetch_l1(Kn + 128 * j);
+        if (128 * (8 + j) < NJ * nx * 8 + 128) prefetch_l1(Kn + 128 * (8 + j));
+      }
+      const size_t ro = (size_t)(t + 1) * nx * 8 + 128 * (j & 1);
+      if (j < 2) prefetch_l1((const char *)xs + ro);
+      else if (j < 4) prefetch_l1((const char *)fs + ro);
+      else if (j < 6) prefetch_l1((const char *)Vfs + ro);
+      else if (j == 6) prefetch_l1(us + (t + 1) * NJ);
+      else prefetch_l1(kb + (t + 1) * NJ);
+      if (j == 0) prefetch_l1(ctx.p_ref + 3);
+      if (j == 1) prefetch_l1(ctx.v_ref + 3);
+    }
     double cst, lam[3];
     coop_action_node<NC, FF, false>(P.mdl, cfg, ct, sm, j, ctx, xt, u, xh, cst, lam, nullptr, false);
     // contact forces of knots 0 / 1 as left by the last rollout that reached them (crocoddyl keeps them in the data)

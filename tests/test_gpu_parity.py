@@ -208,8 +208,8 @@ def test_errors_through_the_abi(built):
 # BASELINE.json full sizes: properties that need no oracle run
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("ff,nc,B,iters,cf", [(False, 1, 4096, 10, 1.0),      # config 3
-                                               (True, 1, 16384, 10, 1.0),      # one GPU's share of config 4
-                                               (True, 3, 4096, 20, 0.75)])     # config 5 (reduced batch)
+                                               (True, 1, 16384, 10, 1.0),      # one scenario of config 4 (4 x 16384)
+                                               (True, 3, 16384, 20, 0.75)])    # config 5: point3d, 25 % free / 75 % contact, 20 iterations
 def test_full_size_properties(built, orc, ff, nc, B, iters, cf):
     N = 50
     cfg, am, inp = make_case(ff, nc, B, N, 1000 * 3 + 11, cf, scenario="actuation_uncertainty" if ff else "flat")
