@@ -110,6 +110,59 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_
   }
 }
 
+// End of one line search for instance b (SolverFDDP::solve after the step-length loop): accept the trial or keep the
+// candidate, regularisation update, stopping test.  `steplength` is the accepted one, or the last one tried.
+FFMPC_DEV void finish_line_search(const Workspace &ws, const ffmpc_config &cfg, int b, int it, bool accepted, bool feasible,
+                                   double steplength, double cost_try, int trial_slot, double d1, double d2) {
+  double preg = ws.preg[b];
+  int wasfeas = ws.wasfeas[b];
+  if (accepted) {
+    wasfeas = feasible ? 1 : 0;
+    ws.wasfeas[b] = wasfeas;
+    ws.feas[b] = (wasfeas || steplength == 1.0) ? 1 : 0;
+    ws.cur[b] = trial_slot;
+    ws.cost[b] = cost_try;
+    ws.recalc[b] = 1;
+  } else {
+    ws.recalc[b] = 0;
+  }
+  bool finished = false;
+  int okflag = 0;
+  if (steplength > cfg.th_stepdec) {
+    preg /= cfg.reg_decfactor;
+    if (preg < cfg.reg_min) preg = cfg.reg_min;
+  }
+  if (steplength <= cfg.th_stepinc) {
+    preg *= cfg.reg_incfactor;
+    if (preg > cfg.reg_max) preg = cfg.reg_max;
+    if (preg == cfg.reg_max) finished = true;
+  }
+  ws.preg[b] = preg;
+  if (!finished) {
+    const double stop = fabs(d1 + 0.5 * d2);
+    ws.stop[b] = stop;
+    if (!ws.fixed_iters && wasfeas && stop < cfg.th_stop) {
+      finished = true;
+      okflag = 1;
+    }
+  }
+  if (finished) {
+    ws.done[b] = 1;
+    ws.ok[b] = okflag;
+    ws.iter[b] = it;
+  } else {
+    ws.iter[b] = it + 1;
+  }
+}
+
+FFMPC_DEV bool accept_step(const ffmpc_config &cfg, bool feasible, double steplength, double dV, double d1, double d2) {
+  const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
+  if (dVexp >= 0.0) return d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp;
+  return !feasible && dV > cfg.th_acceptnegstep * dVexp;
+}
+
+constexpr int TRIAL_REC = 10;  // per (instance, step length) result of a speculative rollout: ok, cost, dv, lam01[6], pad
+
 // ------------------------------------------------------------------------------------------------
 // k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update, ONE step
 // length per launch.  Pass `ia` rolls out alpha = 2^-ia for the instances still searching: pass 0 takes every live
@@ -120,36 +173,38 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_
 // One octet per instance; trial trajectory goes to slot 1 - cur.
 // ------------------------------------------------------------------------------------------------
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia) {
+__global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia_arg) {
   const Workspace &ws = P.ws;
+  const bool spec = ws.spec != 0;
+  const int ia = spec ? (int)blockIdx.y : ia_arg;
   const ffmpc_config &cfg = P.cfg;
   constexpr int nx = FF ? 21 : 14;
   constexpr int cls = (NC == 0) ? 0 : 1;
   const int nfree = ws.counts[0];
   const int base = (NC == 0) ? 0 : nfree;
-  const int cnt = (ia == 0) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[ia * 2 + cls];
+  const int cnt = (ia == 0 || spec) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[ia * 2 + cls];
   if ((int)(blockIdx.x * (blockDim.x >> 3)) >= cnt) return;  // whole block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
   coop_fill_table(P.mdl, P.cfg, ct);
   __syncthreads();
   const int N = ws.N;
-  const int g = global_tid();
+  const int g = global_tid();  // (blockIdx.x, threadIdx.x) only: blockIdx.y is the step length in speculative mode
   const int o = g >> 3, j = g & 7;
   const int jj = j < NJ ? j : NJ - 1;
   const bool act = j < NJ;
   const int lane = (int)(threadIdx.x & 31);
   const unsigned omask = 0xffu << (lane & ~7);
-  const int *items = (ia == 0) ? (ws.perm + base) : (ws.queue + ((size_t)((ia & 1) * 2 + cls)) * ws.B);
+  const int *items = (ia == 0 || spec) ? (ws.perm + base) : (ws.queue + ((size_t)((ia & 1) * 2 + cls)) * ws.B);
   bool valid = o < cnt;
   const int b = items[valid ? o : 0];
-  if (valid && ia == 0 && ws.done[b]) valid = false;
+  if (valid && (ia == 0 || spec) && ws.done[b]) valid = false;
   if (!__any_sync(kFull, valid)) return;
   const int cur = ws.cur[b];
-  const int trial = 1 - cur;
+  const int trial = spec ? (ia + (ia >= cur ? 1 : 0)) : (1 - cur);
   const bool feasible = ws.feas[b] != 0;
   double cost = ws.cost[b];
-  if (ia == 0 && !ws.cost_valid[b]) {
+  if (ia == 0 && !spec && !ws.cost_valid[b]) {
     cost = 0.0;  // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
     for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
   }
@@ -179,6 +234,7 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
   CoopX xh;
   xh.q = ctx.yr_q; xh.v = ctx.yr_v; xh.t = ctx.yr_t;  // x0
   double ct_sum = 0.0, dv_part = 0.0;
+  double lam01[6] = {NAN, NAN, NAN, NAN, NAN, NAN};
   bool failed = false;
   for (int t = 0; t <= N; ++t) {
     CoopX xt;
@@ -236,9 +292,13 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
     coop_action_node<NC, FF, false>(P.mdl, cfg, ct, sm, j, ctx, xt, u, xh, cst, lam, nullptr, false);
     // contact forces of knots 0 / 1 as left by the last rollout that reached them (crocoddyl keeps them in the data)
     if (NC != 0 && t < 2 && valid && j == 0 && !failed) {
-      ws.f_pred[b * 6 + t * 3 + 0] = lam[0];
-      ws.f_pred[b * 6 + t * 3 + 1] = lam[1];
-      ws.f_pred[b * 6 + t * 3 + 2] = lam[2];
+      if (spec) {
+        lam01[t * 3 + 0] = lam[0]; lam01[t * 3 + 1] = lam[1]; lam01[t * 3 + 2] = lam[2];
+      } else {
+        ws.f_pred[b * 6 + t * 3 + 0] = lam[0];
+        ws.f_pred[b * 6 + t * 3 + 1] = lam[1];
+        ws.f_pred[b * 6 + t * 3 + 2] = lam[2];
+      }
     }
     ct_sum += cst;
     bool bad = false;
@@ -249,15 +309,22 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
   const double dv_all = oct_sum(dv_part);  // unconditional: every lane of the warp takes part in the shuffles
   if (!valid || j != 0) return;
   const double dv = feasible ? 0.0 : dv_all;
+  if (ws.spec) {
+    // speculative mode: only record the trial; k_forward_finalize replays the sequential decisions
+    double *tr = ws.trial + ((size_t)b * cfg.n_alphas + ia) * TRIAL_REC;
+    tr[0] = failed ? 0.0 : 1.0;
+    tr[1] = ct_sum;
+    tr[2] = dv;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) tr[3 + i] = lam01[i];
+    return;
+  }
   bool accepted = false;
   double d1 = ws.d1[b], d2 = ws.d2[b];  // keep the values of the last forwardPass that did not throw
   if (!failed) {
-    const double dV = cost - ct_sum;
     d1 = dg + dv;
     d2 = dq - 2.0 * dv;
-    const double dVexp = steplength * (d1 + 0.5 * steplength * d2);
-    if (dVexp >= 0.0) accepted = (d1 < cfg.th_grad || dV > cfg.th_acceptstep * dVexp);
-    else accepted = (!feasible && dV > cfg.th_acceptnegstep * dVexp);
+    accepted = accept_step(cfg, feasible, steplength, cost - ct_sum, d1, d2);
   }
   if (ia == 0) {
     ws.cost_valid[b] = 1;
@@ -271,45 +338,52 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_co
     ws.queue[((size_t)(((ia + 1) & 1) * 2 + cls)) * ws.B + pos] = b;
     return;
   }
-  double preg = ws.preg[b];
-  int wasfeas = ws.wasfeas[b];
-  if (accepted) {
-    wasfeas = feasible ? 1 : 0;
-    ws.wasfeas[b] = wasfeas;
-    ws.feas[b] = (wasfeas || steplength == 1.0) ? 1 : 0;
-    ws.cur[b] = trial;
-    ws.cost[b] = ct_sum;
-    ws.recalc[b] = 1;
-  } else {
-    ws.recalc[b] = 0;
+  finish_line_search(ws, cfg, b, it, accepted, feasible, steplength, ct_sum, trial, d1, d2);
+}
+
+// Speculative line search (small batches: latency matters, the GPU is far from full): ALL step lengths are rolled out at
+// once (k_forward_coop with gridDim.y = n_alphas, one trial slot per step length); this kernel then takes, per instance,
+// exactly the decisions of the sequential loop: trials after the first accepted one "never ran".
+static __global__ void k_forward_finalize(const __grid_constant__ Params P, int it) {
+  const Workspace &ws = P.ws;
+  const ffmpc_config &cfg = P.cfg;
+  const int b = global_tid();
+  if (b >= ws.B || ws.done[b]) return;
+  const int N = ws.N;
+  const int cur = ws.cur[b];
+  const bool feasible = ws.feas[b] != 0;
+  const bool contact = ws.mode[b] == FFMPC_MODE_CONTACT;
+  double cost = ws.cost[b];
+  if (!ws.cost_valid[b]) {
+    cost = 0.0;
+    for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
   }
-  bool finished = false;
-  int okflag = 0;
-  if (steplength > cfg.th_stepdec) {
-    preg /= cfg.reg_decfactor;
-    if (preg < cfg.reg_min) preg = cfg.reg_min;
-  }
-  if (steplength <= cfg.th_stepinc) {
-    preg *= cfg.reg_incfactor;
-    if (preg > cfg.reg_max) preg = cfg.reg_max;
-    if (preg == cfg.reg_max) finished = true;
-  }
-  ws.preg[b] = preg;
-  if (!finished) {
-    const double stop = fabs(d1 + 0.5 * d2);
-    ws.stop[b] = stop;
-    if (!ws.fixed_iters && wasfeas && stop < cfg.th_stop) {
-      finished = true;
-      okflag = 1;
+  const double dg = ws.dg[b], dq = ws.dq[b];
+  double d1 = ws.d1[b], d2 = ws.d2[b], cost_try = 0.0;
+  bool accepted = false;
+  int ia_acc = cfg.n_alphas - 1;
+  for (int ia = 0; ia < cfg.n_alphas && !accepted; ++ia) {
+    const double *tr = ws.trial + ((size_t)b * cfg.n_alphas + ia) * TRIAL_REC;
+    if (contact)
+      for (int i = 0; i < 6; ++i)
+        if (!isnan(tr[3 + i])) ws.f_pred[b * 6 + i] = tr[3 + i];
+    if (tr[0] != 0.0) {
+      const double steplength = ldexp(1.0, -ia);
+      const double dv = feasible ? 0.0 : tr[2];
+      d1 = dg + dv;
+      d2 = dq - 2.0 * dv;
+      if (accept_step(cfg, feasible, steplength, cost - tr[1], d1, d2)) {
+        accepted = true;
+        ia_acc = ia;
+        cost_try = tr[1];
+      }
     }
   }
-  if (finished) {
-    ws.done[b] = 1;
-    ws.ok[b] = okflag;
-    ws.iter[b] = it;
-  } else {
-    ws.iter[b] = it + 1;
-  }
+  ws.cost_valid[b] = 1;
+  ws.cost[b] = cost;
+  ws.d1[b] = d1;
+  ws.d2[b] = d2;
+  finish_line_search(ws, cfg, b, it, accepted, feasible, ldexp(1.0, -ia_acc), cost_try, ia_acc + (ia_acc >= cur ? 1 : 0), d1, d2);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -288,6 +288,11 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   if (const char *e = getenv("FFMPC_COOP")) h->coop = atoi(e) != 0;
   h->lgA_max = h->coop ? 0 : fwd_lanes_log2(max_batch, cfg->n_alphas);
   ws.nslots = 1 + (1 << h->lgA_max);
+  // small batches: speculative line search (all step lengths rolled out at once), one trial slot per step length.
+  // FFMPC_SPEC = 0 / 1 forces the mode (tests exercise both).
+  ws.spec = (h->coop && max_batch <= 512) ? 1 : 0;
+  if (const char *e = getenv("FFMPC_SPEC")) ws.spec = (h->coop && atoi(e) != 0) ? 1 : 0;
+  if (ws.spec) ws.nslots = 1 + cfg->n_alphas;
   DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
   DA(ws.us, (size_t)ws.nslots * B * N * NJ);
   DA(ws.fs, B * (N + 1) * nx);
@@ -302,6 +307,7 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   DA(ws.f_pred, B * 6);
   DA(ws.queue, 4 * B);
   DA(ws.qcount, 64);
+  DA(ws.trial, ws.spec ? B * (size_t)cfg->n_alphas * 10 : 1);
 #undef DA
   if (rc != FFMPC_OK) {
     ffmpc_destroy(h);

@@ -38,6 +38,8 @@ struct Workspace {
   double *f_pred;   // [B,2,3]
   int *queue;       // [2 parity][2 mode buckets][B] instances still in the line search (k_forward_coop)
   int *qcount;      // [32][2] number of queued instances per step-length pass and mode bucket
+  int spec;         // 1: speculative line search (all step lengths at once, small batches), trial slots 1..n_alphas
+  double *trial;    // [B, n_alphas, 10] results of the speculative rollouts
 };
 
 struct Params {

@@ -22,6 +22,21 @@ int launch_forward_coop(const Params &P, int it, cudaStream_t st) {
   const int grid = (int)(((size_t)P.ws.B * 8 + kFwdCoopBlock - 1) / kFwdCoopBlock);
   const bool ff = P.cfg.variant == FFMPC_VARIANT_FF;
   const int nc = P.cfg.contact_nc;
+  if (P.ws.spec) {
+    // latency mode: every step length in one launch (gridDim.y), then the sequential decisions
+    const dim3 g2((unsigned)grid, (unsigned)P.cfg.n_alphas);
+    if (ff) {
+      FFMPC_LAUNCH((k_forward_coop<0, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+      else FFMPC_LAUNCH((k_forward_coop<3, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+    } else {
+      FFMPC_LAUNCH((k_forward_coop<0, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+      else FFMPC_LAUNCH((k_forward_coop<3, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
+    }
+    FFMPC_LAUNCH(k_forward_finalize, (P.ws.B + 127) / 128, 128, 0, st, P, it);
+    return 3;
+  }
   cudaMemsetAsync(P.ws.qcount, 0, 32 * 2 * sizeof(int), st);
   int launches = 0;
   for (int ia = 0; ia < P.cfg.n_alphas; ++ia) {

@@ -57,11 +57,15 @@ def test_emulated_node_kernels_match_oracle(emu, orc, ff, nc, cf):
         assert rel_err(a, b) < 1e-10, k
 
 
-@pytest.mark.parametrize("ff,nc,cf,box", [(False, 1, 1.0, 1), (False, 1, 0.0, 1), (True, 1, 0.5, 1), (True, 3, 1.0, 1), (True, 1, 1.0, 0)])
-def test_emulated_solver_matches_oracle(emu, orc, ff, nc, cf, box):
+# line search: "queue" = one launch per step length with compaction (large batches), "spec" = every step length rolled
+# out at once + k_forward_finalize (handles with max_batch <= 512); FFMPC_SPEC is read by ffmpc_create
+@pytest.mark.parametrize("ff,nc,cf,box,mode", [(False, 1, 1.0, 1, "queue"), (False, 1, 0.0, 1, "spec"), (True, 1, 0.5, 1, "queue"),
+                                               (True, 1, 0.5, 1, "spec"), (True, 3, 1.0, 1, "spec"), (True, 1, 1.0, 0, "queue")])
+def test_emulated_solver_matches_oracle(emu, orc, monkeypatch, ff, nc, cf, box, mode):
     B, N, iters = 5, 12, 6
     cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
     cfg.use_box_fddp = box
+    monkeypatch.setenv("FFMPC_SPEC", "1" if mode == "spec" else "0")
     eng = _engine(emu, cfg, am, B)
     out = eng.solve_host(inp, iters, True)
     eng.close()

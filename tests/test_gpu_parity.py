@@ -117,6 +117,23 @@ def test_ten_fixed_iterations_match_oracle(built, orc, ff, nc, cf):
     assert np.isnan(out["f_pred"][~c]).all()
 
 
+def test_line_search_modes_agree_bitwise(built, monkeypatch):
+    """The queued line search (one launch per step length, large batches) and the speculative one (all step lengths at
+    once, handles with max_batch <= 512) take the same decisions from the same rollouts: bit-identical results."""
+    B, N, iters = 96, 50, 8
+    cfg, am, inp = make_case(True, 1, B, N, 9, 0.8)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("FFMPC_SPEC", mode)
+        eng = _eng(cfg, am, B)
+        res[mode] = eng.solve_host(inp, iters, True)
+        eng.close()
+    for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok"):
+        assert np.array_equal(res["0"][k], res["1"][k]), k
+    c = inp.mode == 1
+    assert np.array_equal(res["0"]["f_pred"][c], res["1"]["f_pred"][c])
+
+
 def test_plain_fddp_and_early_exit(built, orc):
     """use_box_fddp = 0 (`solver="fddp"`, crocoddyl_classical.py:442-445) and the converged early exit."""
     B, N = 32, 30
