@@ -146,6 +146,51 @@ class NodeOut(C.Structure):
     ]
 
 
+class TickPolicy(C.Structure):
+    _fields_ = [
+        ("use_feedback_policy", C.c_int),
+        ("ff_use_tau_interpolation", C.c_int),
+        ("ff_inverse_actuation_model", C.c_int),
+        ("apply_command_filter", C.c_int),
+        ("feedback_gain_scale", C.c_double),
+        ("dt_mpc", C.c_double),
+        ("ff_alpha_ctrl", C.c_double),
+        ("max_solver_cost", C.c_double),
+        ("max_tau_raw_inf", C.c_double),
+        ("fallback_dq_damping", C.c_double),
+        ("tau_trust_inf", C.c_double),
+        ("tau_smoothing_alpha", C.c_double),
+        ("tau_rate_limit", C.c_double * 7),
+    ]
+
+
+class TickIn(C.Structure):
+    _fields_ = [
+        ("B", C.c_int),
+        ("reset", C.c_int),
+        ("mode", C.c_void_p),
+        ("x_now", C.c_void_p),
+        ("p_ref", C.c_void_p),
+        ("v_ref", C.c_void_p),
+        ("x_reg_ref", C.c_void_p),
+        ("tau_bias", C.c_void_p),
+    ]
+
+
+class TickOut(C.Structure):
+    _fields_ = [
+        ("tau_cmd", C.c_void_p),
+        ("tau_raw", C.c_void_p),
+        ("cost", C.c_void_p),
+        ("fn_pred", C.c_void_p),
+        ("iters", C.c_void_p),
+        ("ok", C.c_void_p),
+        ("unstable", C.c_void_p),
+        ("xs", C.c_void_p),
+        ("us", C.c_void_p),
+    ]
+
+
 # every symbol include/ffmpc.h declares (tests check the product library exports all of them)
 EXPORTED_SYMBOLS = [
     "ffmpc_default_config",
@@ -154,6 +199,8 @@ EXPORTED_SYMBOLS = [
     "ffmpc_solve_batch",
     "ffmpc_solve_batch_host",
     "ffmpc_node_eval_host",
+    "ffmpc_tick_batch",
+    "ffmpc_tick_batch_host",
     "ffmpc_last_timing",
     "ffmpc_set_profiling",
     "ffmpc_get_profile",

@@ -282,3 +282,25 @@ def to_abi(cfg, model: PandaModel, q_nom: np.ndarray, R_des: Optional[np.ndarray
     c.n_alphas = 10
     c.boxqp_maxiter, c.boxqp_th_acceptstep, c.boxqp_th_grad, c.boxqp_reg = 100, 0.1, 1e-5, 0.0
     return c
+
+
+def tick_policy(cfg, dt_mpc: Optional[float] = None) -> _abi.TickPolicy:
+    """`ffmpc_tick_policy` of a controller config: the per-tick host logic of `compute_control` the batched tick runs on the
+    device (policy scale, Eq. 14 interpolation, unstable guard, `_safe_tau`).  dt_mpc = sim.dt (default cfg.dt)."""
+    p = _abi.TickPolicy()
+    dt = float(cfg.dt if dt_mpc is None else dt_mpc)
+    p.use_feedback_policy = int(bool(cfg.use_feedback_policy))
+    p.ff_use_tau_interpolation = int(bool(getattr(cfg, "ff_use_tau_interpolation", True)))
+    p.ff_inverse_actuation_model = int(bool(getattr(cfg, "ff_inverse_actuation_model", False)))
+    p.apply_command_filter = int(bool(cfg.apply_command_filter))
+    p.feedback_gain_scale = float(cfg.feedback_gain_scale)
+    p.dt_mpc = dt
+    if getattr(cfg, "ff_alpha_override", None) is not None:
+        p.ff_alpha_ctrl = float(np.clip(float(cfg.ff_alpha_override), 0.0, 0.999999))
+    else:
+        p.ff_alpha_ctrl = float(np.clip(np.exp(-2.0 * np.pi * float(max(getattr(cfg, "ff_cutoff_hz", 0.0), 0.0)) * dt), 0.0, 0.999999))
+    p.max_solver_cost, p.max_tau_raw_inf = float(cfg.max_solver_cost), float(cfg.max_tau_raw_inf)
+    p.fallback_dq_damping = float(cfg.fallback_dq_damping)
+    p.tau_trust_inf, p.tau_smoothing_alpha = float(cfg.tau_trust_inf), float(cfg.tau_smoothing_alpha)
+    _abi.set_array(p.tau_rate_limit, np.asarray(cfg.tau_rate_limit, dtype=float))
+    return p

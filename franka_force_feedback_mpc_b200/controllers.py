@@ -55,10 +55,10 @@ def vertical_down_rotation_mj() -> np.ndarray:
 class _EngineSolver:
     """Default solver: the CUDA engine through the C ABI, B = 1."""
 
-    def __init__(self, cfg_abi, model_abi, device: int = 0):
+    def __init__(self, cfg_abi, model_abi, device: int = 0, _lib=None):
         from .engine import FFMPCEngine
 
-        self.eng = FFMPCEngine(cfg_abi, model_abi, device=device, max_batch=1)
+        self.eng = FFMPCEngine(cfg_abi, model_abi, device=device, max_batch=1, _lib=_lib)
 
     def solve(self, inp: BatchInputs, max_iters: int) -> dict:
         # fixed_iters = False: keep Crocoddyl's converged early exit (solver.solve(xs, us, maxiter, False))

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "ffmpc_launch.h"
+#include "ffmpc_tick.cuh"
 
 using namespace ffmpc;
 
@@ -58,6 +59,10 @@ struct ffmpc_handle {
   double *o_xs = nullptr, *o_us = nullptr, *o_K = nullptr, *o_k = nullptr, *o_cost = nullptr, *o_stop = nullptr, *o_gaps = nullptr,
          *o_fpred = nullptr;
   int *o_iters = nullptr, *o_ok = nullptr;
+  // receding-horizon tick state (ffmpc_tick_batch)
+  TickState tick = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double *d_taubias = nullptr, *o_taucmd = nullptr, *o_tauraw = nullptr, *o_fnpred = nullptr;
+  int *o_unstable = nullptr;
   double last_ms = 0.0;
   int last_launches = 0;
   bool timing_valid = false;
@@ -495,6 +500,123 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
   return FFMPC_OK;
 }
 
+namespace {
+int tick_state(ffmpc_handle *h) {
+  if (h->tick.plan_valid) return FFMPC_OK;
+  const size_t B = (size_t)h->max_batch, N = (size_t)h->N, nx = (size_t)h->nx;
+  int rc = FFMPC_OK;
+#define DA(ptr, count) if (rc == FFMPC_OK) rc = dalloc(h, &(ptr), (count))
+  DA(h->tick.plan_valid, B); DA(h->tick.prev_mode, B); DA(h->tick.tau_prev, B * NJ);
+  DA(h->tick.xs_init, B * (N + 1) * nx); DA(h->tick.us_init, B * N * NJ);
+#undef DA
+  if (rc == FFMPC_OK) {
+    CU(cudaMemset(h->tick.plan_valid, 0, B * sizeof(int)));
+    CU(cudaMemset(h->tick.prev_mode, 0xff, B * sizeof(int)));
+    CU(cudaMemset(h->tick.tau_prev, 0, B * NJ * sizeof(double)));
+  }
+  return rc;
+}
+}  // namespace
+
+int ffmpc_tick_batch(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_policy *pol, int max_iters, int fixed_iters,
+                     const ffmpc_tick_out *out, void *stream) {
+  if (!h || !in || !pol || !out) return fail(FFMPC_ERR_ARG, "null handle / in / policy / out");
+  CU(cudaSetDevice(h->device));
+  if (!in->mode || !in->x_now || !in->p_ref || !in->v_ref || !in->x_reg_ref || !in->tau_bias)
+    return fail(FFMPC_ERR_ARG, "mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias are required");
+  if (!(pol->dt_mpc > 0.0)) return fail(FFMPC_ERR_ARG, "policy.dt_mpc must be > 0");
+  if (int e = tick_state(h)) return e;
+  ffmpc_batch_in bin;
+  bin.B = in->B; bin.mode = in->mode; bin.x0 = in->x_now; bin.p_ref = in->p_ref; bin.v_ref = in->v_ref; bin.x_reg_ref = in->x_reg_ref;
+  bin.tau_ref = nullptr; bin.xs_init = h->tick.xs_init; bin.us_init = h->tick.us_init;
+  if (int e = bind_inputs(h, &bin, max_iters, fixed_iters)) return e;
+  cudaStream_t saved = h->stream;
+  if (stream) h->stream = (cudaStream_t)stream;
+  cudaStream_t st = h->stream;
+  TickArgs A;
+  A.st = h->tick; A.reset = in->reset; A.mode = in->mode; A.x_now = in->x_now; A.tau_bias = in->tau_bias; A.pol = *pol;
+  A.tau_cmd = out->tau_cmd; A.tau_raw = out->tau_raw; A.cost = out->cost; A.fn_pred = out->fn_pred;
+  A.iters = out->iters; A.ok = out->ok; A.unstable = out->unstable;
+  Params P;
+  P.mdl = h->mdl; P.cfg = h->cfg; P.ws = h->ws;
+  const size_t total = (size_t)h->ws.B * (h->N + 1) * h->nx;
+  const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+  FFMPC_LAUNCH(k_tick_prepare, grid, 256, 0, st, h->ws, A);
+  int launches = 0, l2 = 0;
+  int rc = launch_solve(h, max_iters, launches);
+  if (rc == FFMPC_OK) {
+    FFMPC_LAUNCH(k_tick_policy, (h->ws.B + 127) / 128, 128, 0, st, P, A);
+    if (out->xs || out->us) {
+      ffmpc_batch_out bo;
+      std::memset(&bo, 0, sizeof(bo));
+      bo.xs = out->xs; bo.us = out->us;
+      rc = launch_export(h, &bo, l2);
+    }
+  }
+  if (rc == FFMPC_OK && cudaGetLastError() != cudaSuccess) rc = fail(FFMPC_ERR_CUDA, "tick kernel launch failed");
+  h->stream = saved;
+  h->last_launches = launches + l2 + 2;
+  h->timing_valid = false;
+  return rc;
+}
+
+int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_policy *pol, int max_iters, int fixed_iters,
+                          const ffmpc_tick_out *out) {
+  if (!h || !in || !pol || !out) return fail(FFMPC_ERR_ARG, "null handle / in / policy / out");
+  CU(cudaSetDevice(h->device));
+  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
+  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
+  if (!in->mode || !in->x_now || !in->p_ref || !in->v_ref || !in->x_reg_ref || !in->tau_bias)
+    return fail(FFMPC_ERR_ARG, "mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias are required");
+  const size_t Bm = (size_t)h->max_batch, B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx;
+  int rc = FFMPC_OK;
+#define DA(ptr, count) if (rc == FFMPC_OK && !(ptr)) rc = dalloc(h, &(ptr), (count))
+  DA(h->d_mode, Bm); DA(h->d_x0, Bm * nx); DA(h->d_pref, Bm * (N + 1) * 3); DA(h->d_vref, Bm * (N + 1) * 3); DA(h->d_xreg, Bm * 14);
+  DA(h->d_taubias, Bm * NJ);
+  DA(h->o_taucmd, Bm * NJ); DA(h->o_tauraw, Bm * NJ); DA(h->o_fnpred, Bm); DA(h->o_cost, Bm); DA(h->o_iters, Bm); DA(h->o_ok, Bm);
+  DA(h->o_unstable, Bm);
+  if (out->xs) DA(h->o_xs, Bm * (N + 1) * nx);
+  if (out->us) DA(h->o_us, Bm * N * NJ);
+#undef DA
+  if (rc != FFMPC_OK) return rc;
+  cudaStream_t st = h->stream;
+#define H2D(dst, src, count, T) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyHostToDevice, st))
+  H2D(h->d_mode, in->mode, B, int);
+  H2D(h->d_x0, in->x_now, B * nx, double);
+  H2D(h->d_pref, in->p_ref, B * (N + 1) * 3, double);
+  H2D(h->d_vref, in->v_ref, B * (N + 1) * 3, double);
+  H2D(h->d_xreg, in->x_reg_ref, B * 14, double);
+  H2D(h->d_taubias, in->tau_bias, B * NJ, double);
+#undef H2D
+  ffmpc_tick_in din = *in;
+  din.mode = h->d_mode; din.x_now = h->d_x0; din.p_ref = h->d_pref; din.v_ref = h->d_vref; din.x_reg_ref = h->d_xreg; din.tau_bias = h->d_taubias;
+  ffmpc_tick_out dout;
+  dout.tau_cmd = h->o_taucmd; dout.tau_raw = h->o_tauraw; dout.cost = h->o_cost; dout.fn_pred = h->o_fnpred;
+  dout.iters = h->o_iters; dout.ok = h->o_ok; dout.unstable = h->o_unstable;
+  dout.xs = out->xs ? h->o_xs : nullptr; dout.us = out->us ? h->o_us : nullptr;
+  CU(cudaEventRecord(h->ev0, st));
+  rc = ffmpc_tick_batch(h, &din, pol, max_iters, fixed_iters, &dout, nullptr);
+  if (rc != FFMPC_OK) return rc;
+  CU(cudaEventRecord(h->ev1, st));
+#define D2H(dst, src, count, T) if (dst) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyDeviceToHost, st))
+  D2H(out->tau_cmd, h->o_taucmd, B * NJ, double);
+  D2H(out->tau_raw, h->o_tauraw, B * NJ, double);
+  D2H(out->cost, h->o_cost, B, double);
+  D2H(out->fn_pred, h->o_fnpred, B, double);
+  D2H(out->iters, h->o_iters, B, int);
+  D2H(out->ok, h->o_ok, B, int);
+  D2H(out->unstable, h->o_unstable, B, int);
+  D2H(out->xs, h->o_xs, B * (N + 1) * nx, double);
+  D2H(out->us, h->o_us, B * N * NJ, double);
+#undef D2H
+  CU(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  h->last_ms = ms;
+  h->timing_valid = true;
+  return FFMPC_OK;
+}
+
 int ffmpc_last_timing(ffmpc_handle *h, double *kernel_ms, int *launches) {
   if (!h) return fail(FFMPC_ERR_ARG, "null handle");
   if (kernel_ms) *kernel_ms = h->timing_valid ? h->last_ms : -1.0;
@@ -552,6 +674,9 @@ void ffmpc_abi_sizes(int *sizes) {
   sizes[2] = (int)sizeof(ffmpc_batch_in);
   sizes[3] = (int)sizeof(ffmpc_batch_out);
   sizes[4] = (int)sizeof(ffmpc_node_out);
+  sizes[5] = (int)sizeof(ffmpc_tick_policy);
+  sizes[6] = (int)sizeof(ffmpc_tick_in);
+  sizes[7] = (int)sizeof(ffmpc_tick_out);
 }
 
 }  // extern "C"

@@ -32,6 +32,8 @@ def _declare(lib):
     lib.ffmpc_solve_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     lib.ffmpc_solve_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.ffmpc_node_eval_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ffmpc_tick_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    lib.ffmpc_tick_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.ffmpc_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.ffmpc_sync.argtypes = [C.c_void_p]
     lib.ffmpc_set_profiling.argtypes = [C.c_void_p, C.c_int]
@@ -136,6 +138,30 @@ class FFMPCEngine:
             sp = C.c_void_p(stream.cuda_stream)
         self._check(self.lib.ffmpc_solve_batch(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out), sp))
         return t_out
+
+    # ---- receding-horizon tick for the whole batch (ffmpc_tick_batch_host): shift, solve, policy, guard, filter ----
+    def tick_host(self, mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias, policy: _abi.TickPolicy, max_iters: int,
+                  fixed_iters: bool = False, reset: bool = False, want_plan: bool = False) -> dict:
+        mode = np.ascontiguousarray(mode, dtype=np.int32).reshape(-1)
+        B, N, nx = mode.size, self.N, self.nx
+        arrs = dict(x_now=(B, nx), p_ref=(B, N + 1, 3), v_ref=(B, N + 1, 3), x_reg_ref=(B, 14), tau_bias=(B, 7))
+        vals = dict(x_now=x_now, p_ref=p_ref, v_ref=v_ref, x_reg_ref=x_reg_ref, tau_bias=tau_bias)
+        s_in = _abi.TickIn()
+        s_in.B, s_in.reset, s_in.mode = B, int(bool(reset)), ptr(mode)
+        keep = [mode]
+        for k, shp in arrs.items():
+            a = np.ascontiguousarray(vals[k], dtype=np.float64).reshape(shp)
+            keep.append(a)
+            setattr(s_in, k, ptr(a))
+        out = dict(tau_cmd=np.zeros((B, 7)), tau_raw=np.zeros((B, 7)), cost=np.zeros(B), fn_pred=np.zeros(B),
+                   iters=np.zeros(B, np.int32), ok=np.zeros(B, np.int32), unstable=np.zeros(B, np.int32))
+        if want_plan:
+            out["xs"], out["us"] = np.zeros((B, N + 1, nx)), np.zeros((B, N, 7))
+        s_out = _abi.TickOut()
+        for k, a in out.items():
+            setattr(s_out, k, ptr(a))
+        self._check(self.lib.ffmpc_tick_batch_host(self._h, C.byref(s_in), C.byref(policy), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
+        return out
 
     def sync(self):
         self._check(self.lib.ffmpc_sync(self._h))

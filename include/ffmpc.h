@@ -191,6 +191,59 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
                          const int *knot, const double *x, const double *u,
                          const ffmpc_node_out *out);
 
+/* ---- Receding-horizon tick for B controllers at once --------------------------------------
+ * One call = what `compute_control(obs, t)` does around the solve, for every instance of the batch, on the device:
+ *   mode switch -> drop the plan                      crocoddyl_classical.py:321-329
+ *   warm-start shift / cold start (`_shift_guess`)    crocoddyl_classical.py:733-757   (FF :1014-1039)
+ *   solve                                             crocoddyl_classical.py:367       (FF :605)
+ *   feedback policy (`_policy_control`)               crocoddyl_classical.py:759-779   (FF Eq. 14-18, :1041-1093)
+ *   unstable guard                                    crocoddyl_classical.py:393-403
+ *   command filter (`_safe_tau`)                      crocoddyl_classical.py:260-284
+ * The previous plan (xs, us, K of the last solve), the last command and the last mode stay in the handle between
+ * ticks, so a closed-loop sweep needs no host round trip besides x_now in / tau_cmd out.  Solves on every tick
+ * (`mpc_update_steps = 1`, the value of every preset).  Do not interleave ffmpc_solve_batch calls on the same
+ * handle between ticks: they overwrite the stored plan. */
+typedef struct ffmpc_tick_policy {
+  int use_feedback_policy;       /* cfg.use_feedback_policy                                       */
+  int ff_use_tau_interpolation;  /* FF: Eq. 14 interpolation on / off                             */
+  int ff_inverse_actuation_model;/* FF: tau_raw = (tau_des - a tau_hat) / (1 - a), a = alpha_ctrl */
+  int apply_command_filter;      /* trust region + slew limit + smoothing around the last command */
+  double feedback_gain_scale;
+  double dt_mpc;                 /* control period (sim.dt); epsilon = clip(dt_mpc / dt_ocp, 0, 1) */
+  double ff_alpha_ctrl;          /* exp(-2 pi f_c dt_mpc), only with ff_inverse_actuation_model   */
+  double max_solver_cost, max_tau_raw_inf, fallback_dq_damping;
+  double tau_trust_inf, tau_smoothing_alpha;
+  double tau_rate_limit[FFMPC_NJ];
+} ffmpc_tick_policy;
+
+typedef struct ffmpc_tick_in {
+  int B;
+  int reset;               /* != 0: forget every stored plan first (first tick / new episode); then tau_prev = tau_bias */
+  const int *mode;         /* [B] surface mode of this tick                                   */
+  const double *x_now;     /* [B, nx] measured state; FF: (q, v, tau_hat)                      */
+  const double *p_ref;     /* [B, N+1, 3]                                                      */
+  const double *v_ref;     /* [B, N+1, 3]                                                      */
+  const double *x_reg_ref; /* [B, 14]                                                          */
+  const double *tau_bias;  /* [B, 7] obs.tau_bias: fallback torque of the unstable guard       */
+} ffmpc_tick_in;
+
+typedef struct ffmpc_tick_out {  /* every pointer may be NULL */
+  double *tau_cmd;   /* [B, 7] command after the safety filter                                 */
+  double *tau_raw;   /* [B, 7] policy output before guard / filter (FF: tau_des)               */
+  double *cost;      /* [B]                                                                    */
+  double *fn_pred;   /* [B] predicted normal force: classical f_z(knot 0); FF |f_z| blended to t + dt_mpc; NaN in free mode */
+  int *iters, *ok;   /* [B]                                                                    */
+  int *unstable;     /* [B] 1: guard fired, plan dropped                                       */
+  double *xs, *us;   /* [B, N+1, nx], [B, N, 7] the plan (optional)                            */
+} ffmpc_tick_out;
+
+/* DEVICE pointers, stream-ordered. */
+int ffmpc_tick_batch(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_policy *pol, int max_iters, int fixed_iters,
+                     const ffmpc_tick_out *out, void *stream);
+/* HOST pointers: copies in, ticks, copies out, synchronises. */
+int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_policy *pol, int max_iters, int fixed_iters,
+                          const ffmpc_tick_out *out);
+
 /* Device-time (ms) spent in the kernels of the last ffmpc_solve_batch_host call, measured with
  * CUDA events on the solve stream, and the number of kernel launches it made. */
 int ffmpc_last_timing(ffmpc_handle *h, double *kernel_ms, int *launches);

@@ -44,6 +44,9 @@ def test_ctypes_mirror_matches_compiled_structs(built):
     assert sizes[2] == C.sizeof(_abi.BatchIn)
     assert sizes[3] == C.sizeof(_abi.BatchOut)
     assert sizes[4] == C.sizeof(_abi.NodeOut)
+    assert sizes[5] == C.sizeof(_abi.TickPolicy)
+    assert sizes[6] == C.sizeof(_abi.TickIn)
+    assert sizes[7] == C.sizeof(_abi.TickOut)
 
 
 def test_default_config_matches_oracle_default(built, orc):
