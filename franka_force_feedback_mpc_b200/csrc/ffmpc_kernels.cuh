@@ -526,6 +526,10 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
 
   for (int t = N - 1; t >= 0; --t) {
     const double fs_next = (act && t > 0) ? fsb[(t - 1) * n + lane] : 0.0;
+    // BoxQP operands of this knot (nominal control, warm start = stored k_t): issued here so that their global-memory
+    // latency hides behind the Qxx assembly instead of stalling the gain computation
+    const double u0_pre = box ? usb[t * NJ + r7] : 0.0;
+    const double kq_pre = box ? kb[t * NJ + r7] : 0.0;
     rec_wait();
     const double *G = REC + REC_G;
     // (a) Gh[:,c] = dt * G[:,c] ; (b) VE = V Et : row c
@@ -626,33 +630,41 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int k = 0; k < NJ; ++k) qu += (dt * G[k * NZ + 2 * NJ + r7]) * (dt * VX[k] + VX[NJ + k]);
     }
     __syncwarp();  // YS / GT / QXU visible to every lane
-    // (e) Qxx = Pt^T V Pt + Lxx + Y Gh + Gh^T Tt^T, upper-triangular 3x3 block (bI, bJ) per lane
+    // (e) Qxx = Pt^T V Pt + Lxx + Y Gh + Gh^T Tt^T.
+    // (e1) W = Pt^T V Pt + Lxx, column c per lane (the Euler / LPF structure of Pt makes this O(nx) per column with
+    //      compile-time row predicates), written IN PLACE over V: every reader of the old V is past the barrier above.
+    {
+      double wcol[n];
+#pragma unroll
+      for (int i = 0; i < n; ++i) {
+        double wi = V[i * LD + c];
+        if (c >= NJ && c < 2 * NJ) wi += dt * V[i * LD + c - NJ];
+        if (FF && c >= 2 * NJ) wi *= alpha;
+        wcol[i] = wi;
+      }
+#pragma unroll
+      for (int i = n - 1; i >= 0; --i) {
+        double acc = wcol[i];
+        if (i >= NJ && i < 2 * NJ) acc += dt * wcol[i - NJ];
+        if (FF && i >= 2 * NJ) acc *= alpha;
+        wcol[i] = acc + LZZ_AT(i);
+      }
+      __syncwarp();
+      if (act) {
+#pragma unroll
+        for (int i = 0; i < n; ++i) V[i * LD + c] = wcol[i];
+      }
+      __syncwarp();
+    }
+    // (e2) upper-triangular 3x3 block (bI, bJ) per lane: W block + rank-14 update
     double qb[3][3];
     {
-      // Pt^T V Pt: column / row c of Pt picks V[c] (x alpha for the torque block) plus dt V[c-7] on the velocity block
-#pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        const int i = (i0 + r < n) ? i0 + r : n - 1;
-        const bool imid = (i >= NJ && i < 2 * NJ);
-        const double si = (FF && i >= 2 * NJ) ? alpha : 1.0;
-#pragma unroll
-        for (int s2 = 0; s2 < 3; ++s2) {
-          const int cc = (c0 + s2 < n) ? c0 + s2 : n - 1;
-          const bool cmid = (cc >= NJ && cc < 2 * NJ);
-          const double sc2 = (FF && cc >= 2 * NJ) ? alpha : 1.0;
-          double w = V[i * LD + cc];
-          if (cmid) w += dt * V[i * LD + cc - NJ];
-          if (imid) {
-            double w2 = V[(i - NJ) * LD + cc];
-            if (cmid) w2 += dt * V[(i - NJ) * LD + cc - NJ];
-            w += dt * w2;
-          }
-          const int lo = i < cc ? i : cc, hi = i < cc ? cc : i;
-          qb[r][s2] = si * sc2 * w + REC[REC_LZZ + lo * NZ - (lo * (lo - 1)) / 2 + (hi - lo)];
-        }
-      }
       const int ir[3] = {i0, (i0 + 1 < n) ? i0 + 1 : n - 1, (i0 + 2 < n) ? i0 + 2 : n - 1};
       const int cr[3] = {c0, (c0 + 1 < n) ? c0 + 1 : n - 1, (c0 + 2 < n) ? c0 + 2 : n - 1};
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int s2 = 0; s2 < 3; ++s2) qb[r][s2] = V[ir[r] * LD + cr[s2]];
 #pragma unroll
       for (int k = 0; k < 8; k += 2) {
         double yI[3][2], gI[3][2], gJ[3][2], tJ[3][2];
@@ -717,9 +729,9 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
       for (int i = 1; i < NJ; ++i) kv = (r7 == i) ? kvv[i] : kv;
     } else {
       double hi[NJ];
-      const double u0 = usb[t * NJ + r7];
+      const double u0 = u0_pre;
       const double lb = -cfg.tau_limits[r7] - u0, ub = cfg.tau_limits[r7] - u0;
-      double xq = kb[t * NJ + r7];  // warm start = stored k_t (crocoddyl passes k_[t])
+      double xq = kq_pre;  // warm start = stored k_t (crocoddyl passes k_[t])
       unsigned mask;
       if (!dist_boxqp7(cfg, qrow, qu, lb, ub, xq, lane, LL, DI, mask, hi)) { rec_wait(); return false; }
       kv = -xq;
