@@ -49,3 +49,5 @@ if __name__ == "__main__":
         speed(True, 4096); speed(False, 4096); speed(True, 16384); speed(True, 1, reps=5)
     if what == "prof":
         speed(True, 4096, iters=2, reps=1)
+    if what == "lat":
+        speed(True, 1, reps=6)

@@ -259,6 +259,65 @@ def gen_ctrl():
     print("ctrl_golden.npz", len(out), "arrays")
 
 
+def gen_scen():
+    """The reference's ScenarioUncertaintyInjector (src/run/uncertainty_profiles.py) and RunLogger
+    (src/utils/logging.py) executed as they are on seeded inputs -> scen_golden.npz."""
+    import json
+    import tempfile
+
+    from src.run.uncertainty_profiles import ScenarioUncertaintyInjector, UncertaintyProfileConfig, config_for_scenario
+    from src.sim.franka_sim import Observation
+    from src.utils.logging import RunLogger
+
+    out = {}
+    T = 14
+    rng = np.random.default_rng(77)
+    q = rng.normal(0, 1, (T, 7)); dq = rng.normal(0, 1, (T, 7)); bias = rng.normal(0, 5, (T, 7)); cmd = rng.normal(0, 10, (T, 7))
+    out["in_q"], out["in_dq"], out["in_bias"], out["in_cmd"] = q, dq, bias, cmd
+    z7, z3 = np.zeros(7), np.zeros(3)
+    cases = [(0.005, config_for_scenario("actuation_uncertainty", seed=15), 0.2),
+             (0.001, config_for_scenario("actuation_uncertainty", seed=15), 0.2),
+             (0.002, UncertaintyProfileConfig(seed=3, delta_obs_cycles=5, delta_cmd_s=4.0e-3, sigma_tau=0.2, a_min=0.8, a_max=1.2), 0.35),
+             (0.005, UncertaintyProfileConfig(seed=99, delta_obs_cycles=0, delta_cmd_s=0.0), 1.0)]
+    out["case_dt"] = np.array([c[0] for c in cases]); out["case_alpha"] = np.array([c[2] for c in cases])
+    out["case_cfg"] = np.array([[c[1].a_min, c[1].a_max, c[1].b_min, c[1].b_max, c[1].sigma_q, c[1].sigma_dq, c[1].sigma_tau,
+                                 c[1].delta_obs_cycles, c[1].delta_cmd_s, c[1].seed] for c in cases])
+    for i, (dt, cfg, alpha) in enumerate(cases):
+        inj = ScenarioUncertaintyInjector(dt=dt, nu=7, config=cfg, tau_lpf_alpha=alpha)
+        res = {k: [] for k in ("q", "dq", "tau_meas", "tau_meas_filt", "tau_meas_act", "tau_meas_act_filt", "tau_bias", "plant")}
+        for k in range(T):
+            o = Observation(q=q[k], dq=dq[k], tau_meas=z7, tau_meas_filt=z7, tau_meas_act=z7, tau_meas_act_filt=z7, tau_cmd=z7,
+                            tau_act=z7, tau_constraint=z7, tau_total=z7, tau_bias=bias[k], f_contact_world=z3, f_contact_normal=0.0,
+                            f_contact_normal_world_z=0.0, f_contact_tangent=0.0, contact_count_ee=0, contact_count_table=0,
+                            table_normal_world=np.array([0.0, 0.0, 1.0]))
+            d = inj.observation_for_controller(o)
+            for name in res:
+                if name != "plant":
+                    res[name].append(np.array(getattr(d, name)))
+            res["plant"].append(inj.command_for_plant(cmd[k]))
+        for name, v in res.items():
+            out[f"inj{i}_{name}"] = np.array(v)
+        out[f"inj{i}_meta"] = np.array(json.dumps(inj.meta()))
+
+    # RunLogger: a short run with the field kinds the runners log (run_classical.py:452-481)
+    with tempfile.TemporaryDirectory() as tmp:
+        lg = RunLogger(run_name="classical_flat", results_dir=tmp, notes={"scenario": "flat", "scene": "assets/scenes/x.xml"})
+        for k in range(5):
+            lg.log(t=0.005 * (k + 1), ee_pos=q[k, :3].copy(), tau_cmd=cmd[k].copy(), err_tan=float(abs(dq[k, 0])), fn_meas=float(bias[k, 0]),
+                   fn_pred=float("nan") if k == 1 else float(bias[k, 1]), contact=int(k % 2), solver_iters=int(3 + k), big=np.arange(12.0) + k)
+        lg.set_meta(total_time=0.025, dt=0.005, scenario_label="Flat table", benchmark_mode=True, uncertainty_profile=None,
+                    torque_scale=np.ones(7), rms_tangential_error=float(np.sqrt(0.5)), cfg_summary={"horizon": 36, "w": [1.0, 2.0]})
+        lg.save()
+        out["log_csv"] = np.array(open(lg.path_csv, newline="").read())
+        out["log_meta"] = np.array(open(lg.path_meta).read())
+        z = np.load(lg.path_npz, allow_pickle=True)
+        out["log_npz_keys"] = np.array(sorted(z.files))
+        for k in z.files:
+            out[f"log_npz_{k}"] = z[k]
+    np.savez_compressed(os.path.join(GOLD, "scen_golden.npz"), **out)
+    print("scen_golden.npz", len(out), "arrays")
+
+
 def main():
     if not os.path.isdir(REF):
         raise SystemExit(f"{REF} not found: the golden fixtures can only be regenerated where the reference is mounted")
@@ -269,6 +328,7 @@ def main():
     gen_traj()
     gen_misc()
     gen_ctrl()
+    gen_scen()
 
 
 if __name__ == "__main__":
