@@ -99,6 +99,8 @@ class Config(C.Structure):
         ("boxqp_th_acceptstep", C.c_double),
         ("boxqp_th_grad", C.c_double),
         ("boxqp_reg", C.c_double),
+        ("w_friction_cone", C.c_double),
+        ("mu", C.c_double),
     ]
 
 

@@ -225,11 +225,6 @@ def to_abi(cfg, model: PandaModel, q_nom: np.ndarray, R_des: Optional[np.ndarray
     reference's construction-time errors (crocoddyl_classical.py:141-142, 869-870)."""
     ff = isinstance(cfg, ForceFeedbackMPCConfig)
     nc = contact_nc_of(cfg)
-    if nc == 3 and float(cfg.w_friction_cone) > 0.0:
-        raise ValueError(
-            "w_friction_cone > 0 with point3d (ResidualModelContactFrictionCone, crocoddyl_classical.py:678-686) "
-            "is not implemented by the B200 engine (SURVEY.md 8f row f4); both reference runners set it to 0."
-        )
     if int(cfg.horizon) < 1:
         raise ValueError("horizon must be >= 1")
     c = _abi.Config()
@@ -281,6 +276,9 @@ def to_abi(cfg, model: PandaModel, q_nom: np.ndarray, R_des: Optional[np.ndarray
     c.th_stop = 5e-5 if cfg.use_box_fddp else 1e-9
     c.n_alphas = 10
     c.boxqp_maxiter, c.boxqp_th_acceptstep, c.boxqp_th_grad, c.boxqp_reg = 100, 0.1, 1e-5, 0.0
+    # friction cone: only built by the reference for point3d (crocoddyl_classical.py:678)
+    c.w_friction_cone = float(cfg.w_friction_cone) if nc == 3 else 0.0
+    c.mu = float(cfg.mu)
     return c
 
 

@@ -32,6 +32,7 @@ constexpr int CS_T = 0;     // 7 x 12  joint-local transforms (Rl row-major, pl)
 constexpr int CS_J = 84;    // 7 x 6   J_i
 constexpr int CS_DF = 126;  // 7 x 6   dFda_i = Ycrb_i J_i
 constexpr int CS_HS = 0;    // 7 x 22  Gauss-Newton exchange (aliases T / J / DF, all dead by then)
+constexpr int CS_HF = 154;  // 7 x 6   d lambda_x, d lambda_y / d (q_i, v_i, u_i): friction cone only (aliases DF tail / BT, dead by then)
 constexpr int CS_BT = 168;  // 7 x 4   angular part of Bcrb_i^T J_i
 constexpr int CS_JF = 196;  // 7 x 4   Jf_i (frame linear Jacobian column)
 constexpr int CS_FR = 224;  // 32      EE frame block: pf vf wf a_cl Rf v7
@@ -414,6 +415,9 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
 
   // ---------------- dynamics derivatives: own columns q_j, v_j, u_j ----------------
   double dl[3] = {0.0, 0.0, 0.0};  // d lambda_normal / d (q_j, v_j, u_j)
+  // friction cone (point3d, w_friction_cone > 0): the tangential force components enter the cost too
+  const bool fric = (NC == 3) && cfg.w_friction_cone > 0.0;
+  double dlt[2][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};  // d lambda_x, d lambda_y / d (q_j, v_j, u_j)
   if (DIFF) {
     const sv acc = scan_up6(J * (act ? a : 0.0), j);
     const sv at = ab + acc;
@@ -576,11 +580,34 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
         dl[1] = sv_;
         dl[2] = -tr_own[rr];
       }
+      if constexpr (NC == 3) {
+        if (fric) {
+#pragma unroll
+          for (int rr = 0; rr < 2; ++rr) {
+            double sq = 0.0, sv_ = 0.0;
+#pragma unroll
+            for (int k = 0; k < NJ; ++k) {
+              sq += trall[k][rr] * tq[k];
+              sv_ += trall[k][rr] * tv[k];
+            }
+#pragma unroll
+            for (int s2 = 0; s2 < NCm; ++s2) {
+              sq -= Sinv[rr][s2] * comp(dcq, s2);
+              sv_ -= Sinv[rr][s2] * comp(dcv, s2);
+            }
+            dlt[rr][0] = sq;
+            dlt[rr][1] = sv_;
+            dlt[rr][2] = -tr_own[rr];
+          }
+        }
+      }
     }
     if (!in.with_control) {
 #pragma unroll
       for (int i = 0; i < NJ; ++i) Gq[i] = Gv[i] = Gu[i] = 0.0;
       dl[0] = dl[1] = dl[2] = 0.0;
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) dlt[rr][0] = dlt[rr][1] = dlt[rr][2] = 0.0;
     }
     if (wr && act) {
       double *G = rec + REC_G;
@@ -697,7 +724,9 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       cu += 0.5 * rw[9 + k] * wa[k] * wa[k];
     }
   }
-  double fw = 0.0, fg = 0.0;
+  double fw = 0.0, fg = 0.0;                  // force-space Hessian zz / gradient z
+  double fgt[2] = {0.0, 0.0};                 // gradient x, y            (friction cone only)
+  double fwt[4] = {0.0, 0.0, 0.0, 0.0};       // Hessian xx, yy, xz, yz   (friction cone only)
   if (contact) {
     const double lz = in.with_control ? lamv[2] : 0.0;
     if (cfg.w_unilateral > 0.0) {
@@ -713,7 +742,32 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       fg += cfg.w_fn * r;
       fw += cfg.w_fn;
     }
-    if (!in.with_control) { fg = 0.0; fw = 0.0; }
+    // "friction_cone" (crocoddyl_classical.py:678-686): r = A lambda over FrictionCone(I, mu, 4, false), barrier with
+    // ub = -margin on the facet rows (+-1, 0, -mu), (0, +-1, -mu) and lb = +margin on the normal row (:891-904)
+    if constexpr (NC == 3) {
+      if (fric) {
+        const double eps = fmax(cfg.friction_margin, 0.0), wfc = cfg.w_friction_cone, mu = cfg.mu;
+        const double lx = in.with_control ? lamv[0] : 0.0, ly = in.with_control ? lamv[1] : 0.0;
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+          const double cx = (f == 0) ? 1.0 : (f == 2) ? -1.0 : 0.0, cy = (f == 1) ? 1.0 : (f == 3) ? -1.0 : 0.0;
+          double av, Ar, Arr;
+          barrier_act(cx * lx + cy * ly - mu * lz, -INFINITY, -eps, av, Ar, Arr);
+          cu += wfc * av;
+          const double g = wfc * Ar, h = wfc * Arr;
+          fgt[0] += g * cx; fgt[1] += g * cy; fg -= g * mu;
+          fwt[0] += h * cx * cx; fwt[1] += h * cy * cy;          // xx, yy (xy is identically 0: cx cy = 0 on every facet)
+          fwt[2] -= h * cx * mu; fwt[3] -= h * cy * mu;          // xz, yz
+          fw += h * mu * mu;
+        }
+        double av, Ar, Arr;
+        barrier_act(lz, eps, INFINITY, av, Ar, Arr);
+        cu += wfc * av;
+        fg += wfc * Ar;
+        fw += wfc * Arr;
+      }
+    }
+    if (!in.with_control) { fg = 0.0; fw = 0.0; fgt[0] = fgt[1] = 0.0; fwt[0] = fwt[1] = fwt[2] = fwt[3] = 0.0; }
   }
   cuni = cu;
 
@@ -762,9 +816,15 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       for (int r = 0; r < 6; ++r) sv_ += rg[6 + r] * Jv[r];
       if (wr && act) {
         double *Lz = rec + REC_LZ;
-        Lz[j] = sc * (sq + fg * dl[0]) + (eg3 ? eg3[0] : 0.0);
-        Lz[NJ + j] = sc * (sv_ + fg * dl[1]) + (eg3 ? eg3[1] : 0.0);
-        Lz[2 * NJ + j] = sc * (gu + fg * dl[2]) + (eg3 ? eg3[2] : 0.0);
+        double fgq = fg * dl[0], fgv = fg * dl[1], fgu = fg * dl[2];
+        if constexpr (NC == 3) {
+          fgq += fgt[0] * dlt[0][0] + fgt[1] * dlt[1][0];
+          fgv += fgt[0] * dlt[0][1] + fgt[1] * dlt[1][1];
+          fgu += fgt[0] * dlt[0][2] + fgt[1] * dlt[1][2];
+        }
+        Lz[j] = sc * (sq + fgq) + (eg3 ? eg3[0] : 0.0);
+        Lz[NJ + j] = sc * (sv_ + fgv) + (eg3 ? eg3[1] : 0.0);
+        Lz[2 * NJ + j] = sc * (gu + fgu) + (eg3 ? eg3[2] : 0.0);
       }
     }
     // Gauss-Newton Hessian: publish own columns, then every lane forms the entries (row joint i, own columns)
@@ -777,6 +837,14 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       for (int r = 0; r < 6; r += 2) sts2(H + 12 + r, Jv[r], Jv[r + 1]);
       sts2(H + 18, dl[0], dl[1]);
       sts2(H + 20, dl[2], 0.0);
+      if constexpr (NC == 3) {
+        if (fric) {
+          double *HF = sm + CS_HF + 6 * j;
+          sts2(HF, dlt[0][0], dlt[0][1]);
+          sts2(HF + 2, dlt[0][2], dlt[1][0]);
+          sts2(HF + 4, dlt[1][1], dlt[1][2]);
+        }
+      }
     }
     __syncwarp();
     double wq[12], wv[6];
@@ -784,7 +852,22 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
     for (int r = 0; r < 12; ++r) wq[r] = rw[r] * Jq[r];
 #pragma unroll
     for (int r = 0; r < 6; ++r) wv[r] = rw[6 + r] * Jv[r];
-    const double fq = fw * dl[0], fv = fw * dl[1], fu = fw * dl[2];
+    double fq = fw * dl[0], fv = fw * dl[1], fu = fw * dl[2];
+    // friction cone: (force-space Hessian) x (own columns of d lambda), rows x and y; row z gains the xz / yz couplings
+    double ftq[2] = {0.0, 0.0}, ftv[2] = {0.0, 0.0}, ftu[2] = {0.0, 0.0};
+    if constexpr (NC == 3) {
+      if (fric) {
+#pragma unroll
+        for (int a2 = 0; a2 < 2; ++a2) {
+          ftq[a2] = fwt[a2] * dlt[a2][0] + fwt[2 + a2] * dl[0];
+          ftv[a2] = fwt[a2] * dlt[a2][1] + fwt[2 + a2] * dl[1];
+          ftu[a2] = fwt[a2] * dlt[a2][2] + fwt[2 + a2] * dl[2];
+          fq += fwt[2 + a2] * dlt[a2][0];
+          fv += fwt[2 + a2] * dlt[a2][1];
+          fu += fwt[2 + a2] * dlt[a2][2];
+        }
+      }
+    }
     double *Lzz = rec + REC_LZZ;
     const double ehq = eh3 ? eh3[0] : 0.0, ehv = eh3 ? eh3[1] : 0.0, ehu = eh3 ? eh3[2] : 0.0;
 #pragma unroll
@@ -805,7 +888,23 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
         sqv += hqv[6 + r] * wv[r];
         svv += hvv[r] * wv[r];
       }
-      const double squ = di[0] * fu, svu = di[1] * fu, suu = di[2] * fu;
+      double squ = di[0] * fu, svu = di[1] * fu, suu = di[2] * fu;
+      if constexpr (NC == 3) {
+        if (fric) {
+          const double *HF = sm + CS_HF + 6 * i;
+          double dt_[6];
+          lds2(HF, dt_[0], dt_[1]); lds2(HF + 2, dt_[2], dt_[3]); lds2(HF + 4, dt_[4], dt_[5]);
+#pragma unroll
+          for (int a2 = 0; a2 < 2; ++a2) {
+            sqq += dt_[3 * a2] * ftq[a2];
+            sqv += dt_[3 * a2] * ftv[a2];
+            svv += dt_[3 * a2 + 1] * ftv[a2];
+            squ += dt_[3 * a2] * ftu[a2];
+            svu += dt_[3 * a2 + 1] * ftu[a2];
+            suu += dt_[3 * a2 + 2] * ftu[a2];
+          }
+        }
+      }
       if (wr && act) {
         const bool diag = (i == j);
         // row q_i

@@ -111,6 +111,7 @@ int check_cfg(const ffmpc_config *c) {
   if (!(c->dt_ocp > 0.0)) return fail(FFMPC_ERR_ARG, "config.dt_ocp must be > 0");
   if (c->n_alphas < 1 || c->n_alphas > 32) return fail(FFMPC_ERR_ARG, "config.n_alphas out of range");
   if (c->boxqp_maxiter < 1) return fail(FFMPC_ERR_ARG, "config.boxqp_maxiter must be >= 1");
+  if (c->w_friction_cone > 0.0 && !(c->mu >= 0.0)) return fail(FFMPC_ERR_ARG, "config.mu must be >= 0 when w_friction_cone > 0");
   return FFMPC_OK;
 }
 
@@ -257,6 +258,7 @@ void ffmpc_default_config(ffmpc_config *c, int variant) {
   c->th_stop = 5e-5;
   c->n_alphas = 10;
   c->boxqp_maxiter = 100; c->boxqp_th_acceptstep = 0.1; c->boxqp_th_grad = 1e-5; c->boxqp_reg = 0.0;
+  c->w_friction_cone = 0.0; c->mu = 1.0;  // off in every preset of the reference (run_classical.py:292)
 }
 
 int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch, ffmpc_handle **out) {
@@ -270,6 +272,11 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
     return fail(FFMPC_ERR_NO_DEVICE, "no CUDA device visible: the ffmpc engine has no CPU fallback");
   if (device < 0 || device >= ndev) return fail(FFMPC_ERR_ARG, "device index out of range");
   CU(cudaSetDevice(device));
+  {
+    const char *e = getenv("FFMPC_COOP");
+    if (e && atoi(e) == 0 && cfg->contact_nc == 3 && cfg->w_friction_cone > 0.0)
+      return fail(FFMPC_ERR_ARG, "w_friction_cone > 0 needs the lane-cooperative kernels (FFMPC_COOP=0 selects the thread-per-knot ones)");
+  }
   ffmpc_handle *h = new ffmpc_handle();
   h->device = device;
   h->max_batch = max_batch;

@@ -119,6 +119,13 @@ typedef struct ffmpc_config {
   int n_alphas;            /* step lengths 2^-n, n = 0 .. n_alphas-1 (10)                 */
   int boxqp_maxiter;       /* 100                                                         */
   double boxqp_th_acceptstep, boxqp_th_grad, boxqp_reg; /* 0.1, 1e-5, 0                   */
+
+  /* friction cone, point3d only (crocoddyl_classical.py:678-686, 781-788, 891-904, 999-1018):
+   * ResidualModelContactFrictionCone over FrictionCone(R = I, mu, nf = 4, inner_appr = False) -> r = A f with rows
+   * (cos th_i, sin th_i, -mu), th_i = i pi/2, and (0, 0, 1); QuadraticBarrier with ub = -friction_margin on the
+   * four facet rows and lb = +friction_margin on the normal row.  0 = off (every preset of the reference). */
+  double w_friction_cone;
+  double mu;
 } ffmpc_config;
 
 /* Per-batch inputs.  Pointers are DEVICE pointers for ffmpc_solve_batch and HOST pointers for

@@ -464,6 +464,25 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
         add_quad<T>(c, cfg.w_fn, 3, r, aw);
       }
     }
+    if (nc == 3 && cfg.w_friction_cone > 0.0) {  // "friction_cone" (crocoddyl_classical.py:678-686)
+      // FrictionCone(R = I, mu, nf = 4, inner_appr = false) [upstream]: facet rows (-mu n + t_i)^T, t_i = (cos, sin, 0) at
+      // i 2pi/nf, bounds (-inf, 0]; last row n^T, bounds [min_nforce = 0, inf).  Margin: :891-904.
+      const double inf = std::numeric_limits<double>::infinity();
+      const double eps = std::max(cfg.friction_margin, 0.0);
+      const double pi = 3.14159265358979323846;
+      T r[5];
+      double lb[5], ub[5];
+      for (int i = 0; i < 4; ++i) {
+        const double th = 2.0 * pi / 4.0 * i;
+        r[i] = with_control ? T(std::cos(th)) * out.lam[0] + T(std::sin(th)) * out.lam[1] - T(cfg.mu) * out.lam[2] : T(0.0);
+        lb[i] = -inf;
+        ub[i] = 0.0 - eps;
+      }
+      r[4] = with_control ? out.lam[2] : T(0.0);
+      lb[4] = 0.0 + eps;
+      ub[4] = inf;
+      add_barrier<T>(c, cfg.w_friction_cone, 5, r, lb, ub);
+    }
     if (cfg.w_plane_z > 0.0) {  // "plane_z"
       const V3<T> d = k.pf - p_contact;
       const T r[3] = {d.x, d.y, d.z};
@@ -1251,6 +1270,7 @@ void ffmpc_oracle_default_config(ffmpc_config *c, int variant) {
   c->th_stop = 5e-5;  // Box solvers; plain SolverFDDP uses 1e-9
   c->n_alphas = 10;
   c->boxqp_maxiter = 100; c->boxqp_th_acceptstep = 0.1; c->boxqp_th_grad = 1e-5; c->boxqp_reg = 0.0;
+  c->w_friction_cone = 0.0; c->mu = 1.0;
 }
 
 const char *ffmpc_oracle_last_error(void) { return g_err.c_str(); }

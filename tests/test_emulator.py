@@ -107,3 +107,35 @@ def test_emulated_capacity_and_argument_errors(emu):
         eng.solve_host(inp, 2, True)
     assert "max_batch" in str(e.value)
     eng.close()
+
+
+@pytest.mark.parametrize("ff", [False, True])
+def test_emulated_friction_cone_matches_oracle(emu, orc, monkeypatch, ff):
+    """point3d with w_friction_cone > 0 (mu small enough that facets are violated): knot quantities
+    against the oracle, a short solve, and the thread-per-knot kernels refusing the configuration."""
+    from franka_force_feedback_mpc_b200 import engine
+
+    B, N = 6, 8
+    cfg, am, inp = make_case(ff, 3, B, N, 31, 0.8, w_friction_cone=2.0e2, mu=0.3)
+    rng = np.random.default_rng(7)
+    inst = np.repeat(np.arange(B), 3).astype(np.int32)
+    knot = np.tile([0, 3, N], B).astype(np.int32)
+    x = inp.x0[inst] + rng.normal(0, 0.02, (inst.size, inp.nx))
+    u = rng.normal(0, 3.0, (inst.size, 7)) + (inp.x0[inst][:, 14:21] if ff else 0.0)
+    eng = _engine(emu, cfg, am, B)
+    out = eng.node_eval(inp, inst, knot, x, u)
+    ref = orc.node_eval(cfg, am, inp, inst, knot, x, u)
+    cfg0, _, _ = make_case(ff, 3, B, N, 31, 0.8)
+    assert np.abs(ref["Lxx"] - orc.node_eval(cfg0, am, inp, inst, knot, x, u)["Lxx"]).max() > 1.0   # the term is live
+    for k in NODE_KEYS:
+        assert rel_err(out[k], ref[k]) < 1e-10, k
+    if ff:   # (the classical point3d solve amplifies 1-ulp differences to 1e-5 within a few iterations, with or without the cone)
+        got, want = eng.solve_host(inp, 5, True), orc.solve_batch(cfg, am, inp, 5, True)
+        assert np.array_equal(got["iters"], want["iters"]) and np.array_equal(got["ok"], want["ok"])
+        for k in ("xs", "us", "K", "k", "cost"):
+            assert rel_err(got[k], want[k]) < 1e-6, k
+    eng.close()
+    monkeypatch.setenv("FFMPC_COOP", "0")
+    with pytest.raises(engine.FFMPCError) as e:
+        _engine(emu, cfg, am, B)
+    assert "friction" in str(e.value)

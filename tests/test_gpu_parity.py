@@ -287,3 +287,44 @@ def test_against_crocoddyl_golden(built):
         eng.close()
         for k in ("xs", "us", "K", "k", "cost"):
             assert np.quantile(_inst_rel(out[k], g[f"{tag}_{k}"]), 0.5) < 1e-8, (tag, k)
+
+
+@pytest.mark.parametrize("ff", [False, True])
+def test_friction_cone_point3d_matches_oracle(built, orc, ff):
+    """SURVEY.md 8f4 (ResidualModelContactFrictionCone, crocoddyl_classical.py:678-686): knot quantities and one FDDP
+    iteration with the cone on and violated (mu = 0.3), against the oracle; relative tolerances as for the other
+    variants (1e-10 per knot, 1e-8 after one iteration unless the oracle's own rounding sensitivity is larger)."""
+    B, N = 64, 50
+    cfg, am, inp = make_case(ff, 3, B, N, 31, 0.75, w_friction_cone=2.0e2, mu=0.3)
+    rng = np.random.default_rng(7)
+    inst = np.repeat(np.arange(B), 4).astype(np.int32)
+    knot = np.tile([0, 7, N - 1, N], B).astype(np.int32)
+    x = inp.x0[inst] + rng.normal(0, 0.03, (inst.size, inp.nx))
+    u = rng.normal(0, 3.0, (inst.size, 7)) + (inp.x0[inst][:, 14:21] if ff else 0.0)
+    eng = _eng(cfg, am, B)
+    out = eng.node_eval(inp, inst, knot, x, u)
+    ref = orc.node_eval(cfg, am, inp, inst, knot, x, u)
+    cfg0, _, _ = make_case(ff, 3, B, N, 31, 0.75)
+    assert np.abs(ref["Lxx"] - orc.node_eval(cfg0, am, inp, inst, knot, x, u)["Lxx"]).max() > 1.0   # the term is live
+    contact = inp.mode[inst] == 1
+    for k in NODE_KEYS:
+        a, b = (out[k][contact], ref[k][contact]) if k == "force" else (out[k], ref[k])
+        assert rel_err(a, b) < 1e-10, k
+    got = eng.solve_host(inp, 1, True)
+    eng.close()
+    want = orc.solve_batch(cfg, am, inp, 1, True, nthreads=8)
+    assert np.array_equal(got["iters"], want["iters"]) and np.array_equal(got["ok"], want["ok"])
+    # classical point3d is the ill-conditioned variant (JMinvJt damping 1e-8, see test_ten_fixed_iterations_match_oracle) and
+    # the violated cone adds a stiff term: the bar is 1e-8 or, where the oracle itself moves more than that between its
+    # plain and its FMA-contracted build of the same source or under a 1-ulp change of x0 (measured: up to 9e-9), 30x that movement
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+
+    fast, _ = orc.timing_lib()
+    alts = [orc.solve_batch(cfg, am, inp, 1, True, nthreads=8, _use=fast)]
+    rng = np.random.default_rng(0)
+    for _ in range(2):  # one-ulp perturbations of x0
+        x0p = inp.x0 * (1.0 + rng.uniform(-1.0, 1.0, inp.x0.shape) * 2.2e-16)
+        alts.append(orc.solve_batch(cfg, am, BatchInputs(inp.nx, N, inp.mode, x0p, inp.p_ref, inp.v_ref, inp.x_reg_ref), 1, True, nthreads=8))
+    for k in ("K", "k", "cost", "xs", "us"):
+        floor = np.max([_inst_rel(a[k], want[k]) for a in alts], axis=0)
+        assert (_inst_rel(got[k], want[k]) <= np.maximum(1e-8, 30.0 * floor)).all(), k

@@ -150,3 +150,38 @@ def test_warm_start_reproduces_cold_continuation(orc):
     b = orc.solve_batch(cfg, am, warm, 60, False)
     assert rel_err(b["cost"], a["cost"]) < 1e-4
     assert np.abs(b["us"] - a["us"]).max() < 0.05
+
+
+@pytest.mark.parametrize("ff", [False, True])
+def test_friction_cone_cost_from_first_principles(orc, ff):
+    """`friction_cone` = w * QuadraticBarrier(A f) with Crocoddyl's FrictionCone(R = I, mu, nf = 4,
+    inner_appr = False) [upstream]: facet rows (cos th_i, sin th_i, -mu) <= -margin, normal row f_z >= +margin
+    (crocoddyl_classical.py:678-686, 891-904, 999-1018).  The cost it adds must equal that expression evaluated on the
+    oracle's own contact force, and the derivatives with the term on must still match central differences."""
+    B, N, w, mu = 6, 8, 2.0e2, 0.3
+    cfg, am, inp = make_case(ff, 3, B, N, 21, 1.0, w_friction_cone=w, mu=mu)
+    cfg0, _, _ = make_case(ff, 3, B, N, 21, 1.0)
+    assert cfg.w_friction_cone == w and cfg.mu == mu and cfg0.w_friction_cone == 0.0
+    rng = np.random.default_rng(3)
+    inst = np.repeat(np.arange(B), 2).astype(np.int32)
+    knot = np.tile([2, 5], B).astype(np.int32)
+    x = inp.x0[inst] + rng.normal(0, 0.02, (inst.size, inp.nx))
+    u = rng.normal(0, 2.0, (inst.size, 7)) + (inp.x0[inst][:, 14:21] if ff else 0.0)
+    d, d0 = orc.node_eval(cfg, am, inp, inst, knot, x, u), orc.node_eval(cfg0, am, inp, inst, knot, x, u)
+    f = d["force"]
+    assert np.array_equal(f, d0["force"])
+    th = 2.0 * np.pi / 4 * np.arange(4)
+    A = np.vstack([np.stack([np.cos(th), np.sin(th), -mu * np.ones(4)], axis=1), [[0.0, 0.0, 1.0]]])
+    eps = cfg.friction_margin
+    lb = np.array([-np.inf] * 4 + [eps]); ub = np.array([-eps] * 4 + [np.inf])
+    r = f @ A.T
+    a = 0.5 * (np.minimum(r - lb, 0.0) ** 2 + np.maximum(r - ub, 0.0) ** 2).sum(axis=1)
+    assert (a > 1.0).any()                                   # the cone is violated somewhere: the term is live
+    assert np.allclose(d["cost"] - d0["cost"], cfg.dt_ocp * w * a, rtol=1e-9, atol=1e-12)
+    Fx, Fu, Lx, Lu = _fd_node(orc, cfg, am, inp, inst, knot, x, u)
+    assert rel_err(d["Lx"], Lx) < 2e-6 and np.abs(d["Lu"] - Lu).max() < 2e-6 * max(1.0, np.abs(Lu).max())
+    assert np.array_equal(d["Fx"], d0["Fx"]) and not np.allclose(d["Lxx"], d0["Lxx"])
+    assert min(np.linalg.eigvalsh(h).min() for h in d["Lxx"]) > -1e-7 * np.abs(d["Lxx"]).max()
+    # normal_1d never builds the cone (crocoddyl_classical.py:678: nc == 3 only)
+    c1, _, _ = make_case(ff, 1, B, N, 21, 1.0, w_friction_cone=w, mu=mu)
+    assert c1.w_friction_cone == 0.0
