@@ -14,6 +14,9 @@ constexpr int kCoopBlock = 128;
 #ifndef FFMPC_COOP_MINBLOCKS
 #define FFMPC_COOP_MINBLOCKS 3  // resident blocks per SM the register allocation is sized for
 #endif
+#ifndef FFMPC_FWD_MINBLOCKS
+#define FFMPC_FWD_MINBLOCKS 3   // the rollout kernel's register allocation: 128-thread equivalents per SM
+#endif
 constexpr size_t kCoopSmemBytes = (size_t)(CT_SIZE + (kCoopBlock / 8) * CS_SIZE) * sizeof(double);
 // the rollout is latency-bound (51 dependent knots per instance): one warp (4 instances) per block spreads a small
 // line-search queue over all SMs instead of packing it into a few 4-warp blocks
@@ -51,8 +54,6 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_
   if ((long long)blockIdx.x * (kCoopBlock / 8) >= (long long)cnt * (N + 1)) return;  // block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
-  coop_fill_table(P.mdl, P.cfg, ct);
-  __syncthreads();
   const int g = global_tid();
   const int o = g >> 3, j = g & 7;
   const int jj = j < NJ ? j : NJ - 1;
@@ -60,10 +61,13 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_
   int slot = o / (N + 1), t = o - slot * (N + 1);
   bool valid = slot < cnt;
   if (!valid) { slot = 0; t = 0; }
+  // every global operand of the knot (the dependent index chain perm -> done / recalc / cur -> xs, us, references) is
+  // requested before the constant table is built, so that the memory latency hides behind the table fill
   const int b = ws.perm[base + slot];
-  if (valid && (ws.done[b] || !ws.recalc[b])) valid = false;
-  if (!__any_sync(kFull, valid)) return;
-  const size_t bufoff = (size_t)ws.cur[b] * ws.B;
+  const int b_done = ws.done[b], b_recalc = ws.recalc[b], b_cur = ws.cur[b];
+  prefetch_l1(ws.p_ref + ((size_t)b * (N + 1) + t) * 3);
+  prefetch_l1(ws.v_ref + ((size_t)b * (N + 1) + t) * 3);
+  const size_t bufoff = (size_t)b_cur * ws.B;
   const double *xg = ws.xs + ((bufoff + b) * (N + 1) + t) * nx;
   CoopX x, xn;
   x.q = xg[jj];
@@ -81,6 +85,10 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_node_diff_
   ctx.yr_v = x0[NJ + jj];
   ctx.yr_t = FF ? x0[2 * NJ + jj] : 0.0;
   ctx.terminal = (t == N);
+  coop_fill_table(P.mdl, P.cfg, ct);
+  __syncthreads();
+  if (valid && (b_done || !b_recalc)) valid = false;
+  if (!__any_sync(kFull, valid)) return;
   double cost, lam[3];
   double *rec = ws.rec + ((size_t)b * (N + 1) + t) * REC_SIZE;
   coop_action_node<NC, FF, true>(P.mdl, P.cfg, ct, sm, j, ctx, x, u, xn, cost, lam, rec, valid);
@@ -173,7 +181,7 @@ constexpr int TRIAL_REC = 10;  // per (instance, step length) result of a specul
 // One octet per instance; trial trajectory goes to slot 1 - cur.
 // ------------------------------------------------------------------------------------------------
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock, FFMPC_COOP_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia_arg) {
+__global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia_arg) {
   const Workspace &ws = P.ws;
   const bool spec = ws.spec != 0;
   const int ia = spec ? (int)blockIdx.y : ia_arg;

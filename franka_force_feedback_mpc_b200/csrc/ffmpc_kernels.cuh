@@ -416,7 +416,7 @@ template <bool FF> struct BwdLayout {
   static constexpr int oFS = oVX + 24;
   static constexpr int oDI = oFS + 24;   // reciprocal pivots
   static constexpr int oTT = oDI + 8;    // Tt rows (Pt^T V Et), operand of the blocked Qxx assembly
-  static constexpr int oKT = oTT + n * RS;  // K^T rows (K[:, c]), operand of the blocked Vxx update
+  static constexpr int oKT = oTT;        // K^T rows (K[:, c]), operand of the blocked Vxx update: aliases TT (dead once Qxx is assembled)
   static constexpr int TOTAL = oKT + n * RS;  // doubles per warp (even: every warp region stays 16-byte aligned)
   static_assert(n * RS >= 56 && TOTAL % 2 == 0 && oVE % 2 == 0, "layout");
 };
@@ -833,8 +833,16 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
   return true;
 }
 
+// Residency of the Riccati kernel: FFMPC_BWD_WARPS warps (= instances) per block, FFMPC_BWD_MINBLOCKS blocks per SM.
+// Shared memory (16.1 KB per FF warp) allows 14 warps per SM, the register file then allows 144 registers per thread.
+#ifndef FFMPC_BWD_WARPS
+#define FFMPC_BWD_WARPS 4
+#endif
+#ifndef FFMPC_BWD_MINBLOCKS
+#define FFMPC_BWD_MINBLOCKS 3
+#endif
 template <bool FF>
-__global__ void __launch_bounds__(128, 3) k_backward(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(FFMPC_BWD_WARPS * 32, FFMPC_BWD_MINBLOCKS) k_backward(const __grid_constant__ Params P) {
 #ifdef FFMPC_EMU
   double *smem = (double *)emu::S().smem;
 #else

@@ -17,7 +17,7 @@
 
 namespace ffmpc {
 constexpr int kNodeBlock = 128;
-constexpr int kBwdWarps = 4;
+constexpr int kBwdWarps = FFMPC_BWD_WARPS;
 constexpr int kFwdBlock = 64;
 
 // ffmpc_launch_node.cu
