@@ -176,13 +176,13 @@ def _cpu_sample_size(args, rate: float, seconds: float, B: int, nthreads: int) -
     return min(n, B)
 
 
-def cpu_baseline(args, cfg, model, inp, nthreads: int) -> dict:
+def cpu_baseline(args, cfg, model, inp, nthreads: int, seconds: float = 15.0) -> dict:
     """The oracle port timed on the host cores: a bounded sample (about 15 s of CPU work) of the same workload."""
     from oracle import oracle as orc
 
     lib, how = orc.timing_lib()
     rate = _cpu_rate_probe(args, cfg, model, inp, lib, nthreads)
-    sub = inp.slice(np.arange(_cpu_sample_size(args, rate, 15.0, inp.B, nthreads)))
+    sub = inp.slice(np.arange(_cpu_sample_size(args, rate, seconds, inp.B, nthreads)))
     orc.rollout_stats(reset=True, _use=lib)
     t0 = time.perf_counter()
     orc.solve_batch(cfg, model, sub, args.iters, True, nthreads=nthreads, _use=lib)
@@ -382,8 +382,11 @@ def main():
     rollouts = 1.0
     if not args.no_cpu_baseline:
         nthreads = os.cpu_count() or 1
-        cpu = cpu_baseline(args, cfg, model, inp, nthreads)
-        rollouts = cpu.get("rollouts_per_iteration") or 1.0
+        if world == 1:
+            cpu = cpu_baseline(args, cfg, model, inp, nthreads)
+            rollouts = cpu.get("rollouts_per_iteration") or 1.0
+        else:  # the CPU baseline is an N = 1 figure; here a 1 s sample only counts the rollouts of the line search (FLOP model)
+            rollouts = cpu_baseline(args, cfg, model, inp, nthreads, seconds=1.0).get("rollouts_per_iteration") or 1.0
     value = world * B * args.steps / (ms_total * 1e-3)
     e2e_val = world * B * args.steps / e2e_s
     peak_tf = engine.dfma_peak_tflops(local_rank)
