@@ -50,6 +50,8 @@ struct ffmpc_handle {
   ffmpc_model mdl;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t copy_stream = nullptr;  // host API, large batches: device->host copies of the leading chunk (created on first use)
+  cudaEvent_t ev_chunk = nullptr;
   std::vector<void *> allocs;
   Workspace ws;  // device pointers of the internal workspace
   // device staging for the host API
@@ -340,6 +342,8 @@ void ffmpc_destroy(ffmpc_handle *h) {
   for (cudaEvent_t e : h->pev) cudaEventDestroy(e);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ev_chunk) cudaEventDestroy(h->ev_chunk);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -397,36 +401,68 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
   if (in->xs_init) H2D(h->d_xsinit, in->xs_init, B * (N + 1) * nx, double);
   if (in->us_init) H2D(h->d_usinit, in->us_init, B * N * NJ, double);
 #undef H2D
-  ffmpc_batch_in din;
-  din.B = in->B;
-  din.mode = h->d_mode; din.x0 = h->d_x0; din.p_ref = h->d_pref; din.v_ref = h->d_vref; din.x_reg_ref = h->d_xreg;
-  din.tau_ref = in->tau_ref ? h->d_tauref : nullptr;
-  din.xs_init = in->xs_init ? h->d_xsinit : nullptr;
-  din.us_init = in->us_init ? h->d_usinit : nullptr;
-  ffmpc_batch_out dout;
-  dout.xs = out->xs ? h->o_xs : nullptr; dout.us = out->us ? h->o_us : nullptr; dout.K = out->K ? h->o_K : nullptr;
-  dout.k = out->k ? h->o_k : nullptr; dout.cost = out->cost ? h->o_cost : nullptr; dout.stop = out->stop ? h->o_stop : nullptr;
-  dout.gaps = out->gaps ? h->o_gaps : nullptr; dout.f_pred = out->f_pred ? h->o_fpred : nullptr;
-  dout.iters = out->iters ? h->o_iters : nullptr; dout.ok = out->ok ? h->o_ok : nullptr;
-  if (int e = bind_inputs(h, &din, max_iters, fixed_iters)) return e;
+  // Large batches are solved as a leading chunk and a short trailing one: the leading chunk's results (K alone is 73 KB per
+  // instance) travel to the host on a second stream while the trailing chunk is solved, so most of the device->host time hides
+  // behind compute.  The trailing chunk is 1/8 of the batch: its solve time about equals the leading chunk's copy time on
+  // PCIe gen5.  Same kernels, same per-instance arithmetic: results do not depend on the split.  FFMPC_HOST_CHUNK=0 disables it.
+  size_t tail = 0;
+  {
+    size_t min_batch = 16384;  // FFMPC_HOST_CHUNK = n > 0: split batches of at least n instances (tests use small n)
+    if (const char *e = getenv("FFMPC_HOST_CHUNK")) min_batch = (size_t)std::max(atoi(e), 0);
+    if (min_batch >= 2 && B >= min_batch && !h->profiling) {
+      tail = B / 8;
+      if (tail >= 512) tail = ((tail + 511) / 512) * 512;
+      tail = std::min(std::max<size_t>(tail, 1), B - 1);
+    }
+  }
+  if (tail && !h->copy_stream) {
+    if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&h->ev_chunk, cudaEventDisableTiming) != cudaSuccess)
+      return fail(FFMPC_ERR_CUDA, "copy stream / event creation failed");
+  }
   int launches = 0, l2 = 0;
   CU(cudaEventRecord(h->ev0, st));
-  rc = launch_solve(h, max_iters, launches);
-  if (rc == FFMPC_OK) rc = launch_export(h, &dout, l2);
-  CU(cudaEventRecord(h->ev1, st));
-  if (rc != FFMPC_OK) return rc;
-#define D2H(dst, src, count, T) if (dst) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyDeviceToHost, st))
-  D2H(out->xs, h->o_xs, B * (N + 1) * nx, double);
-  D2H(out->us, h->o_us, B * N * NJ, double);
-  D2H(out->K, h->o_K, B * N * NJ * nx, double);
-  D2H(out->k, h->o_k, B * N * NJ, double);
-  D2H(out->cost, h->o_cost, B, double);
-  D2H(out->stop, h->o_stop, B, double);
-  D2H(out->gaps, h->o_gaps, B * (N + 1) * nx, double);
-  D2H(out->f_pred, h->o_fpred, B * 6, double);
-  D2H(out->iters, h->o_iters, B, int);
-  D2H(out->ok, h->o_ok, B, int);
+  for (int c = 0; c < (tail ? 2 : 1); ++c) {
+    const size_t off = (c == 0) ? 0 : B - tail, cnt = tail ? (c == 0 ? B - tail : tail) : B;
+    ffmpc_batch_in din;
+    din.B = (int)cnt;
+    din.mode = h->d_mode + off; din.x0 = h->d_x0 + off * nx; din.p_ref = h->d_pref + off * (N + 1) * 3;
+    din.v_ref = h->d_vref + off * (N + 1) * 3; din.x_reg_ref = h->d_xreg + off * 14;
+    din.tau_ref = in->tau_ref ? h->d_tauref + off * NJ : nullptr;
+    din.xs_init = in->xs_init ? h->d_xsinit + off * (N + 1) * nx : nullptr;
+    din.us_init = in->us_init ? h->d_usinit + off * N * NJ : nullptr;
+    ffmpc_batch_out dout;
+    dout.xs = out->xs ? h->o_xs + off * (N + 1) * nx : nullptr; dout.us = out->us ? h->o_us + off * N * NJ : nullptr;
+    dout.K = out->K ? h->o_K + off * N * NJ * nx : nullptr; dout.k = out->k ? h->o_k + off * N * NJ : nullptr;
+    dout.cost = out->cost ? h->o_cost + off : nullptr; dout.stop = out->stop ? h->o_stop + off : nullptr;
+    dout.gaps = out->gaps ? h->o_gaps + off * (N + 1) * nx : nullptr; dout.f_pred = out->f_pred ? h->o_fpred + off * 6 : nullptr;
+    dout.iters = out->iters ? h->o_iters + off : nullptr; dout.ok = out->ok ? h->o_ok + off : nullptr;
+    if (int e = bind_inputs(h, &din, max_iters, fixed_iters)) return e;
+    rc = launch_solve(h, max_iters, launches);
+    if (rc == FFMPC_OK) rc = launch_export(h, &dout, l2);
+    if (rc != FFMPC_OK) return rc;
+    const bool last = (c == (tail ? 1 : 0));
+    cudaStream_t cs = st;
+    if (last) {
+      CU(cudaEventRecord(h->ev1, st));
+    } else {
+      CU(cudaEventRecord(h->ev_chunk, st));
+      CU(cudaStreamWaitEvent(h->copy_stream, h->ev_chunk, 0));
+      cs = h->copy_stream;
+    }
+#define D2H(dst, src, per, T) if (dst) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyDeviceToHost, cs))
+    D2H(out->xs, h->o_xs, (N + 1) * nx, double);
+    D2H(out->us, h->o_us, N * NJ, double);
+    D2H(out->K, h->o_K, N * NJ * nx, double);
+    D2H(out->k, h->o_k, N * NJ, double);
+    D2H(out->cost, h->o_cost, 1, double);
+    D2H(out->stop, h->o_stop, 1, double);
+    D2H(out->gaps, h->o_gaps, (N + 1) * nx, double);
+    D2H(out->f_pred, h->o_fpred, 6, double);
+    D2H(out->iters, h->o_iters, 1, int);
+    D2H(out->ok, h->o_ok, 1, int);
 #undef D2H
+  }
+  if (tail) CU(cudaStreamSynchronize(h->copy_stream));
   CU(cudaStreamSynchronize(st));
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));

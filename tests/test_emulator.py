@@ -139,3 +139,19 @@ def test_emulated_friction_cone_matches_oracle(emu, orc, monkeypatch, ff):
     with pytest.raises(engine.FFMPCError) as e:
         _engine(emu, cfg, am, B)
     assert "friction" in str(e.value)
+
+
+def test_emulated_host_call_split_is_bitwise_neutral(emu, monkeypatch):
+    """ffmpc_solve_batch_host solves large batches as a leading and a trailing chunk so that the leading chunk's
+    device->host copies overlap the trailing solve: the outputs must not depend on the split (mixed modes, so that the
+    mode buckets of the two chunks differ from those of the whole batch)."""
+    B, N = 20, 8
+    cfg, am, inp = make_case(True, 1, B, N, 9, 0.6)
+    eng = _engine(emu, cfg, am, B)
+    monkeypatch.setenv("FFMPC_HOST_CHUNK", "0")
+    whole = eng.solve_host(inp, 4, True)
+    monkeypatch.setenv("FFMPC_HOST_CHUNK", "8")      # 20 instances -> 18 + 2
+    split = eng.solve_host(inp, 4, True)
+    eng.close()
+    for k in whole:
+        assert np.array_equal(whole[k], split[k], equal_nan=True), k

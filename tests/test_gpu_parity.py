@@ -328,3 +328,18 @@ def test_friction_cone_point3d_matches_oracle(built, orc, ff):
     for k in ("K", "k", "cost", "xs", "us"):
         floor = np.max([_inst_rel(a[k], want[k]) for a in alts], axis=0)
         assert (_inst_rel(got[k], want[k]) <= np.maximum(1e-8, 30.0 * floor)).all(), k
+
+
+def test_host_call_split_is_bitwise_neutral(built, monkeypatch):
+    """ffmpc_solve_batch_host overlaps the device->host copies of a leading chunk with the solve of a trailing one
+    (batches >= 16384; threshold lowered here): outputs must be bit-identical to the unsplit call."""
+    B, N = 2048, 50
+    cfg, am, inp = make_case(True, 1, B, N, 9, 0.75)
+    eng = _eng(cfg, am, B)
+    monkeypatch.setenv("FFMPC_HOST_CHUNK", "0")
+    whole = eng.solve_host(inp, 5, True)
+    monkeypatch.setenv("FFMPC_HOST_CHUNK", "1024")   # 2048 -> 1792 + 256
+    split = eng.solve_host(inp, 5, True)
+    eng.close()
+    for k in whole:
+        assert np.array_equal(whole[k], split[k], equal_nan=True), k
