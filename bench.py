@@ -230,8 +230,16 @@ def run_reference(args, rank: int, world: int):
 
 
 def workload_config(args, B: int, nx: int) -> dict:
+    if args.variant == "ff" and args.contact_model == "normal_1d":
+        which = "BASELINE config 4"                                   # the configuration the metric is quoted on (default)
+    elif args.variant == "classical" and args.contact_model == "normal_1d":
+        which = "BASELINE config 3 shape"
+    elif args.variant == "ff":
+        which = "BASELINE config 5 shape"
+    else:
+        which = "non-BASELINE shape"
     return {
-        "workload": f"{'ForceFeedback' if args.variant == 'ff' else 'Classical'}CrocoddylMPC OCP sweep (BASELINE config 4): "
+        "workload": f"{'ForceFeedback' if args.variant == 'ff' else 'Classical'}CrocoddylMPC OCP sweep ({which}): "
                     f"nx={nx} nu=7 {args.contact_model} contact, horizon {args.horizon}, dt_ocp 0.01, Box-FDDP, "
                     f"{args.iters} fixed iterations, cold start, scenarios {'/'.join(SCENARIOS)}",
         "batch_per_gpu": B, "horizon": args.horizon, "iters": args.iters, "nx": nx, "contact_fraction": args.contact_fraction,
