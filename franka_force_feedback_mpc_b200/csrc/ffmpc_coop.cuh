@@ -49,22 +49,23 @@ FFMPC_DEV double oct_sum(double v) {
 }
 // inclusive prefix sum over the octet (lane j gets sum of lanes 0..j)
 FFMPC_DEV double oct_scan_up(double v, int j) {
+  // masked add as one DFMA (fma(1, t, v) == v + t exactly; a lane without a source receives its own, finite, value)
   double t = __shfl_up_sync(kFull, v, 1, 8);
-  if (j >= 1) v += t;
+  v = fma(j >= 1 ? 1.0 : 0.0, t, v);
   t = __shfl_up_sync(kFull, v, 2, 8);
-  if (j >= 2) v += t;
+  v = fma(j >= 2 ? 1.0 : 0.0, t, v);
   t = __shfl_up_sync(kFull, v, 4, 8);
-  if (j >= 4) v += t;
+  v = fma(j >= 4 ? 1.0 : 0.0, t, v);
   return v;
 }
 // inclusive suffix sum (lane j gets sum of lanes j..7)
 FFMPC_DEV double oct_scan_down(double v, int j) {
   double t = __shfl_down_sync(kFull, v, 1, 8);
-  if (j + 1 < 8) v += t;
+  v = fma(j + 1 < 8 ? 1.0 : 0.0, t, v);
   t = __shfl_down_sync(kFull, v, 2, 8);
-  if (j + 2 < 8) v += t;
+  v = fma(j + 2 < 8 ? 1.0 : 0.0, t, v);
   t = __shfl_down_sync(kFull, v, 4, 8);
-  if (j + 4 < 8) v += t;
+  v = fma(j + 4 < 8 ? 1.0 : 0.0, t, v);
   return v;
 }
 FFMPC_DEV v3 scan_up3(const v3 &a, int j) { return mk3(oct_scan_up(a.x, j), oct_scan_up(a.y, j), oct_scan_up(a.z, j)); }

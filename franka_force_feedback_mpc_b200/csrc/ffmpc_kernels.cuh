@@ -635,13 +635,12 @@ FFMPC_DEV bool backward_sweep(const Params &P, int b, double *sm, double preg, b
     //      compile-time row predicates), written IN PLACE over V: every reader of the old V is past the barrier above.
     {
       double wcol[n];
+      // per-lane factors instead of per-entry selects (x 1.0 and + 0.0 * finite are exact: same bits as the branchy form)
+      const bool vcol = c >= NJ && c < 2 * NJ;
+      const double m_dt = vcol ? dt : 0.0, m_al = (FF && c >= 2 * NJ) ? alpha : 1.0;
+      const int c2 = vcol ? c - NJ : c;
 #pragma unroll
-      for (int i = 0; i < n; ++i) {
-        double wi = V[i * LD + c];
-        if (c >= NJ && c < 2 * NJ) wi += dt * V[i * LD + c - NJ];
-        if (FF && c >= 2 * NJ) wi *= alpha;
-        wcol[i] = wi;
-      }
+      for (int i = 0; i < n; ++i) wcol[i] = fma(m_dt, V[i * LD + c2], V[i * LD + c]) * m_al;
 #pragma unroll
       for (int i = n - 1; i >= 0; --i) {
         double acc = wcol[i];
