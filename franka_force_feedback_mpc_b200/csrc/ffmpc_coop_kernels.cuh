@@ -263,11 +263,13 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
       // K dx: lane j multiplies its own three columns of every row, the reduce-scatter hands row a to lane a
       double pr[8];
       const double *Kt = Kb + (size_t)t * NJ * nx;
+      // the padding lane contributes nothing: zero its dx once instead of selecting every partial product
+      const double mq = act ? dxq : 0.0, mv = act ? dxv : 0.0, mt = act ? dxt : 0.0;
 #pragma unroll
       for (int a = 0; a < NJ; ++a) {
-        double s = Kt[a * nx + jj] * dxq + Kt[a * nx + NJ + jj] * dxv;
-        if (FF) s += Kt[a * nx + 2 * NJ + jj] * dxt;
-        pr[a] = act ? s : 0.0;
+        double s = Kt[a * nx + jj] * mq + Kt[a * nx + NJ + jj] * mv;
+        if (FF) s += Kt[a * nx + 2 * NJ + jj] * mt;
+        pr[a] = s;
       }
       pr[7] = 0.0;
       const double kd = oct_reduce_scatter8(pr, j);
