@@ -193,10 +193,20 @@ class TickOut(C.Structure):
     ]
 
 
+LS_AUTO, LS_QUEUE, LS_SPECULATIVE = 0, 1, 2
+LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE}
+
+
+class Options(C.Structure):
+    _fields_ = [("line_search", C.c_int), ("host_chunks", C.c_int), ("reserved", C.c_int * 6)]
+
+
 # every symbol include/ffmpc.h declares (tests check the product library exports all of them)
 EXPORTED_SYMBOLS = [
     "ffmpc_default_config",
+    "ffmpc_default_options",
     "ffmpc_create",
+    "ffmpc_create_ex",
     "ffmpc_destroy",
     "ffmpc_solve_batch",
     "ffmpc_solve_batch_host",

@@ -1,8 +1,7 @@
 // ffmpc_coop.cuh -- lane-cooperative evaluation of ONE action-model knot: 8 lanes ("octet") per knot,
 // 4 knots per warp.  Lane j < 7 owns joint j (its transform, Jacobian column, velocity, inertia, and the
-// columns j / 7+j / 14+j of every 21-wide derivative); lane 7 carries zeros.  Same mathematics as the
-// scalar dam_node / action_node of ffmpc_node.cuh (which stays as the single-thread statement of the
-// formulas and is what tests/host_emul checks this file against), redistributed so that
+// columns j / 7+j / 14+j of every 21-wide derivative); lane 7 carries zeros.  The world-frame recursions of
+// ffmpc_math.cuh, distributed so that
 //   * serial-chain recursions become width-8 shuffle scans (prefix: velocities / accelerations,
 //     suffix: composite inertias / forces / B operators),
 //   * all-to-all products (CRBA, RNEA derivative blocks, KKT products, Gauss-Newton Hessian) read the
@@ -15,7 +14,7 @@
 // octets without work run on dummy data with their writes disabled.
 #pragma once
 
-#include "ffmpc_node.cuh"
+#include "ffmpc_math.cuh"
 
 namespace ffmpc {
 
@@ -611,13 +610,16 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       for (int rr = 0; rr < 2; ++rr) dlt[rr][0] = dlt[rr][1] = dlt[rr][2] = 0.0;
     }
     if (wr && act) {
-      double *G = rec + REC_G;
-#pragma unroll
-      for (int i = 0; i < NJ; ++i) {
-        G[i * NZ + j] = Gq[i];
-        G[i * NZ + NJ + j] = Gv[i];
-        G[i * NZ + 2 * NJ + j] = Gu[i];
-      }
+      // the record holds Gh = dt * d a/d z in the operand layout of the Riccati MMAs: the eight entries (k = 0..7) of
+      // column 7a + j are one 64-byte chunk [k & 3][k >> 2] (rec_gh), written as four 128-bit stores per tile
+      const double dtg = cfg.dt_ocp;
+      double *gh = rec + REC_GH + 8 * j;
+      sts2(gh + 0, dtg * Gq[0], dtg * Gq[4]); sts2(gh + 2, dtg * Gq[1], dtg * Gq[5]);
+      sts2(gh + 4, dtg * Gq[2], dtg * Gq[6]); sts2(gh + 6, dtg * Gq[3], 0.0);
+      sts2(gh + 64, dtg * Gv[0], dtg * Gv[4]); sts2(gh + 66, dtg * Gv[1], dtg * Gv[5]);
+      sts2(gh + 68, dtg * Gv[2], dtg * Gv[6]); sts2(gh + 70, dtg * Gv[3], 0.0);
+      sts2(gh + 128, dtg * Gu[0], dtg * Gu[4]); sts2(gh + 130, dtg * Gu[1], dtg * Gu[5]);
+      sts2(gh + 132, dtg * Gu[2], dtg * Gu[6]); sts2(gh + 134, dtg * Gu[3], 0.0);
     }
   }
 
@@ -816,16 +818,15 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
 #pragma unroll
       for (int r = 0; r < 6; ++r) sv_ += rg[6 + r] * Jv[r];
       if (wr && act) {
-        double *Lz = rec + REC_LZ;
         double fgq = fg * dl[0], fgv = fg * dl[1], fgu = fg * dl[2];
         if constexpr (NC == 3) {
           fgq += fgt[0] * dlt[0][0] + fgt[1] * dlt[1][0];
           fgv += fgt[0] * dlt[0][1] + fgt[1] * dlt[1][1];
           fgu += fgt[0] * dlt[0][2] + fgt[1] * dlt[1][2];
         }
-        Lz[j] = sc * (sq + fgq) + (eg3 ? eg3[0] : 0.0);
-        Lz[NJ + j] = sc * (sv_ + fgv) + (eg3 ? eg3[1] : 0.0);
-        Lz[2 * NJ + j] = sc * (gu + fgu) + (eg3 ? eg3[2] : 0.0);
+        rec[rec_lz(0, j)] = sc * (sq + fgq) + (eg3 ? eg3[0] : 0.0);
+        rec[rec_lz(1, j)] = sc * (sv_ + fgv) + (eg3 ? eg3[1] : 0.0);
+        rec[rec_lz(2, j)] = sc * (gu + fgu) + (eg3 ? eg3[2] : 0.0);
       }
     }
     // Gauss-Newton Hessian: publish own columns, then every lane forms the entries (row joint i, own columns)
@@ -869,8 +870,8 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
         }
       }
     }
-    double *Lzz = rec + REC_LZZ;
     const double ehq = eh3 ? eh3[0] : 0.0, ehv = eh3 ? eh3[1] : 0.0, ehu = eh3 ? eh3[2] : 0.0;
+    double pend_q = 0.0, pend_v = 0.0, pend_u = 0.0;  // even-row entries of the diagonal tiles waiting for their pair
 #pragma unroll
     for (int i = 0; i < NJ; ++i) {
       const double *H = sm + CS_HS + 22 * i;
@@ -908,15 +909,24 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
       }
       if (wr && act) {
         const bool diag = (i == j);
-        // row q_i
-        if (i <= j) Lzz[sym_idx(i, j)] = sc * (sqq + (diag ? hq : 0.0)) + (diag ? ehq : 0.0);
-        Lzz[sym_idx(i, NJ + j)] = sc * sqv;
-        Lzz[sym_idx(i, 2 * NJ + j)] = sc * squ;
-        // row v_i
-        if (i <= j) Lzz[sym_idx(NJ + i, NJ + j)] = sc * (svv + (diag ? hv_ : 0.0)) + (diag ? ehv : 0.0);
-        Lzz[sym_idx(NJ + i, 2 * NJ + j)] = sc * svu;
-        // row u_i
-        if (i <= j) Lzz[sym_idx(2 * NJ + i, 2 * NJ + j)] = sc * (suu + (diag ? hu : 0.0)) + (diag ? ehu : 0.0);
+        // Tiles are row-major 8x8 (the MMA accumulator layout).  Off-diagonal tiles: entry (i, j), lanes contiguous.
+        // Diagonal tiles are symmetric: the lane writes ROW j (= its column) as 128-bit pairs (i, i + 1).
+        const double hqq = sc * (sqq + (diag ? hq : 0.0)) + (diag ? ehq : 0.0);
+        const double hvv = sc * (svv + (diag ? hv_ : 0.0)) + (diag ? ehv : 0.0);
+        const double huu = sc * (suu + (diag ? hu : 0.0)) + (diag ? ehu : 0.0);
+        rec[rec_lzz(0, i, 1, j)] = sc * sqv;
+        rec[rec_lzz(0, i, 2, j)] = sc * squ;
+        rec[rec_lzz(1, i, 2, j)] = sc * svu;
+        if (i & 1) {
+          sts2(rec + rec_lzz(0, j, 0, i - 1), pend_q, hqq);
+          sts2(rec + rec_lzz(1, j, 1, i - 1), pend_v, hvv);
+          sts2(rec + rec_lzz(2, j, 2, i - 1), pend_u, huu);
+        } else if (i == NJ - 1) {
+          sts2(rec + rec_lzz(0, j, 0, i), hqq, 0.0);
+          sts2(rec + rec_lzz(1, j, 1, i), hvv, 0.0);
+          sts2(rec + rec_lzz(2, j, 2, i), huu, 0.0);
+        }
+        pend_q = hqq; pend_v = hvv; pend_u = huu;
       }
     }
   }

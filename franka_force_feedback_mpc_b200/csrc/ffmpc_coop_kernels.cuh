@@ -256,7 +256,9 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
       xw[j] = xt.q;
       xw[NJ + j] = xt.v;
       if (FF) xw[2 * NJ + j] = xt.t;
-      dv_part += vft[j] * dxq + vft[NJ + j] * dxv + (FF ? vft[2 * NJ + j] * dxt : 0.0);  // -fs_t^T Vxx_t (xs_t - xs_try_t)
+      // -fs_t^T Vxx_t (xs_t - xs_try_t): enters the expected improvement only while gaps are open (the sweep stores
+      // Vxx fs only then)
+      if (!feasible) dv_part += vft[j] * dxq + vft[NJ + j] * dxv + (FF ? vft[2 * NJ + j] * dxt : 0.0);
     }
     double u = 0.0;
     if (t < N) {
@@ -466,22 +468,24 @@ __global__ void k_node_expand(const __grid_constant__ Params P, NodeEvalCoopArgs
   const double dt = P.cfg.dt_ocp;
   const double alpha = fmin(fmax(P.cfg.ff_alpha, 0.0), 0.999999), beta = 1.0 - alpha;
   const bool running = FF || (t != ws.N);
+  // the record holds Gh = dt * d a/d z: row r of the position block of Fz is dt * Gh[r], of the velocity block Gh[r]
+  auto gh = [&](int r, int j) { return rec[rec_gh(r, j / NJ, j % NJ)]; };
   for (int i = 0; i < nx; ++i) {
     for (int j = 0; j < nx; ++j) {
       double fx = (i == j) ? 1.0 : 0.0;
       if (i < 14) {
         const int r = i % NJ;
-        const double sc = (i < NJ) ? dt * dt : dt;
+        const double sc = (i < NJ) ? dt : 1.0;
         if (running) {
-          fx += sc * rec[REC_G + r * NZ + j];
+          fx += sc * gh(r, j);
           if (i < NJ && j == NJ + i) fx += dt;
         }
-        if (j >= 14) fx = running ? sc * rec[REC_G + r * NZ + j] : 0.0;
+        if (j >= 14) fx = running ? sc * gh(r, j) : 0.0;
       } else {
         fx = (i == j) ? alpha : 0.0;
       }
       if (A.Fx) A.Fx[((size_t)m * nx + i) * nx + j] = fx;
-      if (A.Lxx) A.Lxx[((size_t)m * nx + i) * nx + j] = rec[REC_LZZ + sym_idx_any(i, j)];
+      if (A.Lxx) A.Lxx[((size_t)m * nx + i) * nx + j] = rec[rec_lzz_any(i, j)];
     }
     for (int a = 0; a < NJ; ++a) {
       double fu, lxu;
@@ -490,19 +494,19 @@ __global__ void k_node_expand(const __grid_constant__ Params P, NodeEvalCoopArgs
         lxu = 0.0;
       } else {
         const int r = i % NJ;
-        const double sc = (i < NJ) ? dt * dt : dt;
-        fu = running ? sc * rec[REC_G + r * NZ + 14 + a] : 0.0;
-        lxu = rec[REC_LZZ + sym_idx_any(i, 14 + a)];
+        const double sc = (i < NJ) ? dt : 1.0;
+        fu = running ? sc * gh(r, 14 + a) : 0.0;
+        lxu = rec[rec_lzz_any(i, 14 + a)];
       }
       if (A.Fu) A.Fu[((size_t)m * nx + i) * NJ + a] = fu;
       if (A.Lxu) A.Lxu[((size_t)m * nx + i) * NJ + a] = lxu;
     }
-    if (A.Lx) A.Lx[(size_t)m * nx + i] = rec[REC_LZ + i];
+    if (A.Lx) A.Lx[(size_t)m * nx + i] = rec[rec_lz_any(i)];
   }
   for (int a = 0; a < NJ; ++a) {
-    if (A.Lu) A.Lu[(size_t)m * NJ + a] = FF ? rec[REC_LW + a] : rec[REC_LZ + 14 + a];
+    if (A.Lu) A.Lu[(size_t)m * NJ + a] = FF ? rec[REC_LW + a] : rec[rec_lz_any(14 + a)];
     for (int c = 0; c < NJ; ++c)
-      if (A.Luu) A.Luu[((size_t)m * NJ + a) * NJ + c] = FF ? ((a == c) ? rec[REC_LWW + a] : 0.0) : rec[REC_LZZ + sym_idx_any(14 + a, 14 + c)];
+      if (A.Luu) A.Luu[((size_t)m * NJ + a) * NJ + c] = FF ? ((a == c) ? rec[REC_LWW + a] : 0.0) : rec[rec_lzz_any(14 + a, 14 + c)];
   }
 }
 

@@ -44,8 +44,7 @@ struct ffmpc_handle {
   int device = 0;
   int max_batch = 0;
   int N = 0, nx = 0;
-  int lgA_max = 0;  // log2 of the line-search lanes per instance the trajectory slots were sized for
-  bool coop = true; // lane-cooperative knot evaluation (8 lanes per knot); FFMPC_COOP=0 selects the thread-per-knot kernels
+  ffmpc_options opt;  // resolved options (line search mode, host-call chunking)
   ffmpc_config cfg;
   ffmpc_model mdl;
   cudaStream_t stream = nullptr;
@@ -85,24 +84,6 @@ template <class T> int dalloc(ffmpc_handle *h, T **p, size_t count) {
   h->allocs.push_back(q);
   *p = (T *)q;
   return FFMPC_OK;
-}
-
-// Lanes per instance of the parallel line search (k_forward).  The rollout is sequential in the horizon, so a
-// small batch cannot fill the GPU with one thread per instance: spread the step lengths over lanes until about
-// 64k threads exist; large batches keep 2 lanes (less speculative work, still no 10-deep divergence).
-// FFMPC_FWD_LANES overrides (1, 2, 4, ... 32) for experiments.
-int fwd_lanes_log2(int batch, int n_alphas) {
-  int lg;
-  if (batch >= 32768) lg = 1;
-  else if (batch >= 8192) lg = 2;
-  else if (batch >= 2048) lg = 3;
-  else lg = 4;
-  if (const char *e = getenv("FFMPC_FWD_LANES")) {
-    const int a = atoi(e);
-    if (a >= 1 && a <= 32) { lg = 0; while ((1 << lg) < a) ++lg; }
-  }
-  while (lg > 0 && (1 << (lg - 1)) >= n_alphas) --lg;  // never more lanes than step lengths (rounded up to 2^k)
-  return lg;
 }
 
 int check_cfg(const ffmpc_config *c) {
@@ -158,8 +139,7 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
 #ifdef FFMPC_EMU
     if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: node_diff\n", it);
 #endif
-    if (h->coop) launch_node_diff_coop(P, st);
-    else launch_node_diff(P, st);
+    launch_node_diff_coop(P, st);
     if (int e = mark(h, FFMPC_FAM_NODE_DIFF, 2)) return e;
 #ifdef FFMPC_EMU
     if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: backward\n", it);
@@ -169,9 +149,7 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
 #ifdef FFMPC_EMU
     if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: forward\n", it);
 #endif
-    int nfwd = 2;
-    if (h->coop) nfwd = launch_forward_coop(P, it, st);
-    else launch_forward(P, it, std::min(h->lgA_max, fwd_lanes_log2(B, h->cfg.n_alphas)), st);
+    const int nfwd = launch_forward_coop(P, it, st);
     if (int e = mark(h, FFMPC_FAM_FORWARD, nfwd)) return e;
     launches += 3 + nfwd;
   }
@@ -263,7 +241,18 @@ void ffmpc_default_config(ffmpc_config *c, int variant) {
   c->w_friction_cone = 0.0; c->mu = 1.0;  // off in every preset of the reference (run_classical.py:292)
 }
 
+void ffmpc_default_options(ffmpc_options *o) {
+  std::memset(o, 0, sizeof(*o));
+  o->line_search = FFMPC_LS_AUTO;
+  o->host_chunks = 0;
+}
+
 int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch, ffmpc_handle **out) {
+  return ffmpc_create_ex(cfg, model, device, max_batch, nullptr, out);
+}
+
+int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch, const ffmpc_options *opt,
+                    ffmpc_handle **out) {
   if (!out) return fail(FFMPC_ERR_ARG, "null out handle");
   *out = nullptr;
   if (int e = check_cfg(cfg)) return e;
@@ -274,12 +263,13 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
     return fail(FFMPC_ERR_NO_DEVICE, "no CUDA device visible: the ffmpc engine has no CPU fallback");
   if (device < 0 || device >= ndev) return fail(FFMPC_ERR_ARG, "device index out of range");
   CU(cudaSetDevice(device));
-  {
-    const char *e = getenv("FFMPC_COOP");
-    if (e && atoi(e) == 0 && cfg->contact_nc == 3 && cfg->w_friction_cone > 0.0)
-      return fail(FFMPC_ERR_ARG, "w_friction_cone > 0 needs the lane-cooperative kernels (FFMPC_COOP=0 selects the thread-per-knot ones)");
-  }
+  ffmpc_options o;
+  ffmpc_default_options(&o);
+  if (opt) o = *opt;
+  if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_SPECULATIVE) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
+  if (o.host_chunks < 0 || o.host_chunks > 64) return fail(FFMPC_ERR_ARG, "options.host_chunks out of range (0 = auto, 1 .. 64)");
   ffmpc_handle *h = new ffmpc_handle();
+  h->opt = o;
   h->device = device;
   h->max_batch = max_batch;
   h->cfg = *cfg;
@@ -298,14 +288,10 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   DA(ws.tau_ref, B * NJ);
   DA(ws.perm, B);
   DA(ws.counts, 2);
-  // parallel line search: A = 2^lgA lanes per instance, each with its own trial slot (see k_forward)
-  if (const char *e = getenv("FFMPC_COOP")) h->coop = atoi(e) != 0;
-  h->lgA_max = h->coop ? 0 : fwd_lanes_log2(max_batch, cfg->n_alphas);
-  ws.nslots = 1 + (1 << h->lgA_max);
-  // small batches: speculative line search (all step lengths rolled out at once), one trial slot per step length.
-  // FFMPC_SPEC = 0 / 1 forces the mode (tests exercise both).
-  ws.spec = (h->coop && max_batch <= 512) ? 1 : 0;
-  if (const char *e = getenv("FFMPC_SPEC")) ws.spec = (h->coop && atoi(e) != 0) ? 1 : 0;
+  // line search: accepted + one trial slot (queue mode: one launch per step length over the compacted queue of rejected
+  // instances); small batches roll every step length out at once (speculative mode: one trial slot per step length)
+  ws.nslots = 2;
+  ws.spec = (h->opt.line_search == FFMPC_LS_SPECULATIVE || (h->opt.line_search == FFMPC_LS_AUTO && max_batch <= 512)) ? 1 : 0;
   if (ws.spec) ws.nslots = 1 + cfg->n_alphas;
   DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
   DA(ws.us, (size_t)ws.nslots * B * N * NJ);
@@ -326,6 +312,11 @@ int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, 
   if (rc != FFMPC_OK) {
     ffmpc_destroy(h);
     return rc;
+  }
+  // the padding entries of the knot records are never written again (ffmpc_math.cuh: record layout)
+  if (cudaMemset(ws.rec, 0, B * (N + 1) * REC_SIZE * sizeof(double)) != cudaSuccess) {
+    ffmpc_destroy(h);
+    return fail(FFMPC_ERR_CUDA, "cudaMemset(records) failed");
   }
   if (prepare_backward() != 0 || prepare_coop_node() != 0 || prepare_coop_fwd() != 0) {
     ffmpc_destroy(h);
@@ -401,28 +392,35 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
   if (in->xs_init) H2D(h->d_xsinit, in->xs_init, B * (N + 1) * nx, double);
   if (in->us_init) H2D(h->d_usinit, in->us_init, B * N * NJ, double);
 #undef H2D
-  // Large batches are solved as a leading chunk and a short trailing one: the leading chunk's results (K alone is 73 KB per
-  // instance) travel to the host on a second stream while the trailing chunk is solved, so most of the device->host time hides
-  // behind compute.  The trailing chunk is 1/8 of the batch: its solve time about equals the leading chunk's copy time on
-  // PCIe gen5.  Same kernels, same per-instance arithmetic: results do not depend on the split.  FFMPC_HOST_CHUNK=0 disables it.
-  size_t tail = 0;
+  // Large batches are solved in chunks: a chunk's results (K alone is 73 KB per instance) travel to the host on a second
+  // stream while the next chunk is solved, so most of the device->host time hides behind compute.  options.host_chunks:
+  // 1 = unsplit, k > 1 = k equal chunks, 0 (auto) = a leading 7/8 and a trailing 1/8 for batches of >= 16384 instances (the
+  // trailing solve about equals the leading chunk's copy time on PCIe gen5).  Same kernels, same per-instance arithmetic:
+  // results do not depend on the split.
+  std::vector<size_t> chunks;
   {
-    size_t min_batch = 16384;  // FFMPC_HOST_CHUNK = n > 0: split batches of at least n instances (tests use small n)
-    if (const char *e = getenv("FFMPC_HOST_CHUNK")) min_batch = (size_t)std::max(atoi(e), 0);
-    if (min_batch >= 2 && B >= min_batch && !h->profiling) {
-      tail = B / 8;
-      if (tail >= 512) tail = ((tail + 511) / 512) * 512;
+    const int k = h->profiling ? 1 : h->opt.host_chunks;
+    if (k == 0 && B >= 16384) {
+      size_t tail = ((B / 8 + 511) / 512) * 512;
       tail = std::min(std::max<size_t>(tail, 1), B - 1);
+      chunks = {B - tail, tail};
+    } else if (k > 1 && B >= (size_t)k) {
+      const size_t per = (B + k - 1) / k;
+      for (size_t off = 0; off < B; off += per) chunks.push_back(std::min(per, B - off));
+    } else {
+      chunks = {B};
     }
   }
-  if (tail && !h->copy_stream) {
+  const bool split = chunks.size() > 1;
+  if (split && !h->copy_stream) {
     if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&h->ev_chunk, cudaEventDisableTiming) != cudaSuccess)
       return fail(FFMPC_ERR_CUDA, "copy stream / event creation failed");
   }
-  int launches = 0, l2 = 0;
+  int launches = 0;
   CU(cudaEventRecord(h->ev0, st));
-  for (int c = 0; c < (tail ? 2 : 1); ++c) {
-    const size_t off = (c == 0) ? 0 : B - tail, cnt = tail ? (c == 0 ? B - tail : tail) : B;
+  size_t off = 0;
+  for (size_t c = 0; c < chunks.size(); ++c) {
+    const size_t cnt = chunks[c];
     ffmpc_batch_in din;
     din.B = (int)cnt;
     din.mode = h->d_mode + off; din.x0 = h->d_x0 + off * nx; din.p_ref = h->d_pref + off * (N + 1) * 3;
@@ -437,14 +435,17 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
     dout.gaps = out->gaps ? h->o_gaps + off * (N + 1) * nx : nullptr; dout.f_pred = out->f_pred ? h->o_fpred + off * 6 : nullptr;
     dout.iters = out->iters ? h->o_iters + off : nullptr; dout.ok = out->ok ? h->o_ok + off : nullptr;
     if (int e = bind_inputs(h, &din, max_iters, fixed_iters)) return e;
-    rc = launch_solve(h, max_iters, launches);
+    int l1 = 0, l2 = 0;
+    rc = launch_solve(h, max_iters, l1);
     if (rc == FFMPC_OK) rc = launch_export(h, &dout, l2);
     if (rc != FFMPC_OK) return rc;
-    const bool last = (c == (tail ? 1 : 0));
+    launches += l1 + l2;
+    const bool last = (c + 1 == chunks.size());
     cudaStream_t cs = st;
     if (last) {
       CU(cudaEventRecord(h->ev1, st));
     } else {
+      // the copy stream takes this chunk's results as soon as its export is done; the solve stream goes on with the next chunk
       CU(cudaEventRecord(h->ev_chunk, st));
       CU(cudaStreamWaitEvent(h->copy_stream, h->ev_chunk, 0));
       cs = h->copy_stream;
@@ -461,13 +462,14 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
     D2H(out->iters, h->o_iters, 1, int);
     D2H(out->ok, h->o_ok, 1, int);
 #undef D2H
+    off += cnt;
   }
-  if (tail) CU(cudaStreamSynchronize(h->copy_stream));
+  if (split) CU(cudaStreamSynchronize(h->copy_stream));
   CU(cudaStreamSynchronize(st));
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
   h->last_ms = ms;
-  h->last_launches = launches + l2;
+  h->last_launches = launches;
   h->timing_valid = true;
   return FFMPC_OK;
 }
@@ -528,8 +530,7 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
   P.cfg = h->cfg;
   P.ws = h->ws;
   FFMPC_LAUNCH(k_init_state, (in->B + 127) / 128, 128, 0, st, P);  // resolves tau_ref
-  if (h->coop) launch_node_eval_coop(P, A, d_rec, st);
-  else launch_node_eval(P, A, st);
+  launch_node_eval_coop(P, A, d_rec, st);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess) { cleanup(); return fail(FFMPC_ERR_CUDA, std::string("node_eval launch: ") + cudaGetErrorString(le)); }
   auto down = [&](void *dst, const void *src, size_t bytes) { if (dst) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st); };

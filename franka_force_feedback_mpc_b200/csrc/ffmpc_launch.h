@@ -16,18 +16,14 @@
 #endif
 
 namespace ffmpc {
-constexpr int kNodeBlock = 128;
+#ifndef FFMPC_BWD_WARPS
+#define FFMPC_BWD_WARPS 4   // warps (= instances) per block of the Riccati kernel
+#endif
 constexpr int kBwdWarps = FFMPC_BWD_WARPS;
-constexpr int kFwdBlock = 64;
 
-// ffmpc_launch_node.cu
-void launch_node_diff(const Params &P, cudaStream_t st);
-void launch_node_eval(const Params &P, const NodeEvalArgs &A, cudaStream_t st);
 // ffmpc_launch_bwd.cu
 int prepare_backward();
 void launch_backward(const Params &P, cudaStream_t st);
-// ffmpc_launch_fwd.cu
-void launch_forward(const Params &P, int it, int lgA, cudaStream_t st);
 // ffmpc_launch_coop_node.cu / ffmpc_launch_coop_fwd.cu  (lane-cooperative knot evaluation, ffmpc_coop.cuh)
 int prepare_coop_node();
 int prepare_coop_fwd();

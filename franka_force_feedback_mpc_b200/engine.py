@@ -27,6 +27,9 @@ def _declare(lib):
     lib.ffmpc_last_error.restype = C.c_char_p
     lib.ffmpc_version.restype = C.c_char_p
     lib.ffmpc_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    lib.ffmpc_create_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.ffmpc_default_options.argtypes = [C.c_void_p]
+    lib.ffmpc_default_options.restype = None
     lib.ffmpc_destroy.argtypes = [C.c_void_p]
     lib.ffmpc_destroy.restype = None
     lib.ffmpc_solve_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -70,9 +73,11 @@ def dfma_peak_tflops(device: int = 0) -> float:
 
 
 class FFMPCEngine:
-    """One handle per GPU (``ffmpc_create``)."""
+    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec"; ``host_chunks``: how
+    ``solve_host`` pipelines result copies against compute (0 = auto).  Both only schedule work: results are bit-identical."""
 
-    def __init__(self, cfg: _abi.Config, model: _abi.Model, device: int = 0, max_batch: int = 1, _lib=None):
+    def __init__(self, cfg: _abi.Config, model: _abi.Model, device: int = 0, max_batch: int = 1, _lib=None,
+                 line_search: str = "auto", host_chunks: int = 0):
         self.lib = _lib if _lib is not None else load_library()
         self.cfg, self.model = cfg, model
         self.N = int(cfg.horizon)
@@ -80,7 +85,11 @@ class FFMPCEngine:
         self.max_batch = int(max_batch)
         self.device = int(device)
         self._h = C.c_void_p()
-        rc = self.lib.ffmpc_create(C.byref(cfg), C.byref(model), self.device, self.max_batch, C.byref(self._h))
+        opt = _abi.Options()
+        self.lib.ffmpc_default_options(C.byref(opt))
+        opt.line_search = _abi.LINE_SEARCH_MODES[line_search]
+        opt.host_chunks = int(host_chunks)
+        rc = self.lib.ffmpc_create_ex(C.byref(cfg), C.byref(model), self.device, self.max_batch, C.byref(opt), C.byref(self._h))
         self._check(rc)
 
     def _check(self, rc):

@@ -177,9 +177,26 @@ typedef struct ffmpc_handle ffmpc_handle;
 /* Fills the crocoddyl solver defaults and the reference's dataclass defaults. */
 void ffmpc_default_config(ffmpc_config *cfg, int variant);
 
+/* Execution options of a handle (how the work is scheduled on the GPU; never what is computed: every mode gives
+ * bit-identical results). */
+#define FFMPC_LS_AUTO 0        /* by max_batch: speculative for <= 512 instances, queued above                       */
+#define FFMPC_LS_QUEUE 1       /* one launch per step length over the compacted queue of instances that rejected the
+                                  previous one (same trial sequence as the loop of SolverFDDP::solve)                  */
+#define FFMPC_LS_SPECULATIVE 2 /* every step length rolled out in one launch, decisions replayed in order (latency)   */
+typedef struct ffmpc_options {
+  int line_search; /* FFMPC_LS_*                                                                                     */
+  int host_chunks; /* ffmpc_solve_batch_host: 0 = auto, 1 = unsplit, k > 1 = k chunks whose device->host copies
+                      overlap the next chunk's solve                                                                 */
+  int reserved[6];
+} ffmpc_options;
+void ffmpc_default_options(ffmpc_options *opt);
+
 /* One handle per GPU; owns workspace for up to max_batch instances; not thread-safe. */
 int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch,
                  ffmpc_handle **out);
+/* Same with explicit options (NULL = defaults). */
+int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch,
+                    const ffmpc_options *opt, ffmpc_handle **out);
 void ffmpc_destroy(ffmpc_handle *h);
 
 /* Batched solve, DEVICE pointers, stream-ordered (returns after enqueueing; `stream` is a

@@ -49,6 +49,7 @@ struct State {
   std::vector<int> warp_count, warp_gen;
   int blk_count = 0, blk_gen = 0;
   std::vector<uint64_t> xch;  // [warps*32]
+  std::vector<uint64_t> xch2; // [warps*32] second payload (all-gather of two values: tensor-core MMA emulation)
   std::vector<int> pred;      // [warps*32]
   char *smem = nullptr;
   size_t smem_cap = 0;
@@ -122,6 +123,7 @@ inline void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function
   s.warp_count.assign(nw, 0);
   s.warp_gen.assign(nw, 0);
   s.xch.assign((size_t)nw * 32, 0);
+  s.xch2.assign((size_t)nw * 32, 0);
   s.pred.assign((size_t)nw * 32, 0);
   for (unsigned b = 0; b < grid.x * grid.y * grid.z; ++b) {
     s.bid = dim3(b % grid.x, (b / grid.x) % grid.y, b / (grid.x * grid.y));
@@ -171,6 +173,19 @@ template <class T> inline T shfl_idx(T v, int src_lane) {
   T r = (src_lane >= 0 && src_lane < nwd) ? from_bits<T>(s.xch[w * 32 + src_lane]) : v;
   warp_sync();
   return r;
+}
+// every lane receives the (a, b) pair of all 32 lanes of its warp: two barriers instead of one shuffle per element
+inline void allgather2(double a, double b, double *all_a, double *all_b) {
+  State &s = S();
+  const int w = s.cur / 32, lane = s.cur % 32;
+  s.xch[w * 32 + lane] = to_bits(a);
+  s.xch2[w * 32 + lane] = to_bits(b);
+  warp_sync();
+  for (int i = 0; i < 32; ++i) {
+    all_a[i] = from_bits<double>(s.xch[w * 32 + i]);
+    all_b[i] = from_bits<double>(s.xch2[w * 32 + i]);
+  }
+  warp_sync();
 }
 inline unsigned ballot(int p) {
   State &s = S();

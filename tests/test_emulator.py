@@ -26,10 +26,10 @@ def emu():
     return lib
 
 
-def _engine(emu, cfg, am, B):
+def _engine(emu, cfg, am, B, **opt):
     from franka_force_feedback_mpc_b200 import engine
 
-    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B, _lib=emu)
+    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B, _lib=emu, **opt)
 
 
 @pytest.mark.parametrize("ff", [False, True])
@@ -58,15 +58,14 @@ def test_emulated_node_kernels_match_oracle(emu, orc, ff, nc, cf):
 
 
 # line search: "queue" = one launch per step length with compaction (large batches), "spec" = every step length rolled
-# out at once + k_forward_finalize (handles with max_batch <= 512); FFMPC_SPEC is read by ffmpc_create
+# out at once + k_forward_finalize (handles with max_batch <= 512); ffmpc_options.line_search
 @pytest.mark.parametrize("ff,nc,cf,box,mode", [(False, 1, 1.0, 1, "queue"), (False, 1, 0.0, 1, "spec"), (True, 1, 0.5, 1, "queue"),
                                                (True, 1, 0.5, 1, "spec"), (True, 3, 1.0, 1, "spec"), (True, 1, 1.0, 0, "queue")])
-def test_emulated_solver_matches_oracle(emu, orc, monkeypatch, ff, nc, cf, box, mode):
+def test_emulated_solver_matches_oracle(emu, orc, ff, nc, cf, box, mode):
     B, N, iters = 5, 12, 6
     cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
     cfg.use_box_fddp = box
-    monkeypatch.setenv("FFMPC_SPEC", "1" if mode == "spec" else "0")
-    eng = _engine(emu, cfg, am, B)
+    eng = _engine(emu, cfg, am, B, line_search=mode)
     out = eng.solve_host(inp, iters, True)
     eng.close()
     ref = orc.solve_batch(cfg, am, inp, iters, True)
@@ -110,9 +109,9 @@ def test_emulated_capacity_and_argument_errors(emu):
 
 
 @pytest.mark.parametrize("ff", [False, True])
-def test_emulated_friction_cone_matches_oracle(emu, orc, monkeypatch, ff):
+def test_emulated_friction_cone_matches_oracle(emu, orc, ff):
     """point3d with w_friction_cone > 0 (mu small enough that facets are violated): knot quantities
-    against the oracle, a short solve, and the thread-per-knot kernels refusing the configuration."""
+    against the oracle and a short solve."""
     from franka_force_feedback_mpc_b200 import engine
 
     B, N = 6, 8
@@ -135,22 +134,18 @@ def test_emulated_friction_cone_matches_oracle(emu, orc, monkeypatch, ff):
         for k in ("xs", "us", "K", "k", "cost"):
             assert rel_err(got[k], want[k]) < 1e-6, k
     eng.close()
-    monkeypatch.setenv("FFMPC_COOP", "0")
-    with pytest.raises(engine.FFMPCError) as e:
-        _engine(emu, cfg, am, B)
-    assert "friction" in str(e.value)
 
 
-def test_emulated_host_call_split_is_bitwise_neutral(emu, monkeypatch):
-    """ffmpc_solve_batch_host solves large batches as a leading and a trailing chunk so that the leading chunk's
-    device->host copies overlap the trailing solve: the outputs must not depend on the split (mixed modes, so that the
-    mode buckets of the two chunks differ from those of the whole batch)."""
+def test_emulated_host_call_split_is_bitwise_neutral(emu):
+    """ffmpc_solve_batch_host solves large batches in chunks so that a chunk's device->host copies overlap the next
+    chunk's solve (ffmpc_options.host_chunks): the outputs must not depend on the split (mixed modes, so that the mode
+    buckets of the chunks differ from those of the whole batch)."""
     B, N = 20, 8
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.6)
-    eng = _engine(emu, cfg, am, B)
-    monkeypatch.setenv("FFMPC_HOST_CHUNK", "0")
+    eng = _engine(emu, cfg, am, B, host_chunks=1)
     whole = eng.solve_host(inp, 4, True)
-    monkeypatch.setenv("FFMPC_HOST_CHUNK", "8")      # 20 instances -> 18 + 2
+    eng.close()
+    eng = _engine(emu, cfg, am, B, host_chunks=3)      # 20 instances -> 7 + 7 + 6
     split = eng.solve_host(inp, 4, True)
     eng.close()
     for k in whole:

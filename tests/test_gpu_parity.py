@@ -27,10 +27,10 @@ NODE_KEYS = ("xnext", "cost", "force", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Lu
 VARIANTS = [(False, 1, 1.0), (False, 1, 0.0), (False, 3, 0.5), (True, 1, 1.0), (True, 1, 0.0), (True, 3, 0.5)]
 
 
-def _eng(cfg, am, B):
+def _eng(cfg, am, B, **opt):
     from franka_force_feedback_mpc_b200 import engine
 
-    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B)
+    return engine.FFMPCEngine(cfg, am, device=0, max_batch=B, **opt)
 
 
 def _inst_rel(a, b):
@@ -117,15 +117,14 @@ def test_ten_fixed_iterations_match_oracle(built, orc, ff, nc, cf):
     assert np.isnan(out["f_pred"][~c]).all()
 
 
-def test_line_search_modes_agree_bitwise(built, monkeypatch):
+def test_line_search_modes_agree_bitwise(built):
     """The queued line search (one launch per step length, large batches) and the speculative one (all step lengths at
     once, handles with max_batch <= 512) take the same decisions from the same rollouts: bit-identical results."""
     B, N, iters = 96, 50, 8
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.8)
     res = {}
-    for mode in ("0", "1"):
-        monkeypatch.setenv("FFMPC_SPEC", mode)
-        eng = _eng(cfg, am, B)
+    for mode, ls in (("0", "queue"), ("1", "spec")):
+        eng = _eng(cfg, am, B, line_search=ls)
         res[mode] = eng.solve_host(inp, iters, True)
         eng.close()
     for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok"):
@@ -330,15 +329,15 @@ def test_friction_cone_point3d_matches_oracle(built, orc, ff):
         assert (_inst_rel(got[k], want[k]) <= np.maximum(1e-8, 30.0 * floor)).all(), k
 
 
-def test_host_call_split_is_bitwise_neutral(built, monkeypatch):
-    """ffmpc_solve_batch_host overlaps the device->host copies of a leading chunk with the solve of a trailing one
-    (batches >= 16384; threshold lowered here): outputs must be bit-identical to the unsplit call."""
+def test_host_call_split_is_bitwise_neutral(built):
+    """ffmpc_solve_batch_host overlaps the device->host copies of a chunk with the solve of the next one
+    (ffmpc_options.host_chunks): outputs must be bit-identical to the unsplit call."""
     B, N = 2048, 50
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.75)
-    eng = _eng(cfg, am, B)
-    monkeypatch.setenv("FFMPC_HOST_CHUNK", "0")
+    eng = _eng(cfg, am, B, host_chunks=1)
     whole = eng.solve_host(inp, 5, True)
-    monkeypatch.setenv("FFMPC_HOST_CHUNK", "1024")   # 2048 -> 1792 + 256
+    eng.close()
+    eng = _eng(cfg, am, B, host_chunks=5)   # 2048 -> 410 x 4 + 408
     split = eng.solve_host(inp, 5, True)
     eng.close()
     for k in whole:
