@@ -176,6 +176,7 @@ class TickIn(C.Structure):
         ("v_ref", C.c_void_p),
         ("x_reg_ref", C.c_void_p),
         ("tau_bias", C.c_void_p),
+        ("tau_ref", C.c_void_p),
     ]
 
 
@@ -198,7 +199,11 @@ LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE}
 
 
 class Options(C.Structure):
-    _fields_ = [("line_search", C.c_int), ("host_chunks", C.c_int), ("reserved", C.c_int * 6)]
+    _fields_ = [("line_search", C.c_int), ("sub_batches", C.c_int), ("reserved", C.c_int * 6)]
+
+
+class Info(C.Structure):
+    _fields_ = [("sub_batches", C.c_int), ("sub_batch_capacity", C.c_int), ("line_search", C.c_int), ("reserved", C.c_int * 5)]
 
 
 # every symbol include/ffmpc.h declares (tests check the product library exports all of them)
@@ -218,6 +223,7 @@ EXPORTED_SYMBOLS = [
     "ffmpc_get_profile",
     "ffmpc_dfma_peak",
     "ffmpc_sync",
+    "ffmpc_get_info",
     "ffmpc_last_error",
     "ffmpc_version",
 ]

@@ -5,6 +5,13 @@
 // there is NO CPU execution path: without a CUDA device ffmpc_create fails with FFMPC_ERR_NO_DEVICE.
 // (tests/host_emul compiles this same file against a fiber-based CUDA emulator, FFMPC_EMU, purely to
 // run the kernel sources in CPU CI; that build is a separate test-only library.)
+//
+// Scheduling.  Instances are independent, so a batch is solved as up to `sub_batches` contiguous SUB-BATCHES, each
+// with its own workspace and its own CUDA stream; stream priorities fall with the sub-batch index.  The early
+// sub-batches therefore run first, the later ones fill what they leave idle (the last wave of every kernel, the late
+// line-search passes that hold a few percent of the instances and run at the latency of one serial rollout), and in
+// the host API the results of a finished sub-batch cross PCIe while the others are still being solved.  Sub-batching
+// only schedules: the per-instance arithmetic, and so every result bit, is the same for any split.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -33,9 +40,14 @@ int fail(int code, const std::string &msg) {
     if (e_ != cudaSuccess) return fail(FFMPC_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
   } while (0)
 
-struct DevBuf {
-  void *p = nullptr;
-  size_t bytes = 0;
+struct Sub {
+  Workspace ws;                  // device pointers of this sub-batch's workspace (capacity `cap` instances)
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;    // recorded after the last kernel of the sub-batch
+};
+
+struct Chunk {
+  size_t off, cnt;
 };
 
 }  // namespace
@@ -44,15 +56,14 @@ struct ffmpc_handle {
   int device = 0;
   int max_batch = 0;
   int N = 0, nx = 0;
-  ffmpc_options opt;  // resolved options (line search mode, host-call chunking)
+  int cap = 0;        // instances per sub-batch workspace
+  ffmpc_options opt;  // resolved options
   ffmpc_config cfg;
   ffmpc_model mdl;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  cudaStream_t copy_stream = nullptr;  // host API, large batches: device->host copies of the leading chunk (created on first use)
-  cudaEvent_t ev_chunk = nullptr;
+  cudaStream_t stream = nullptr;  // main stream: ordering point of the host API, profiling runs
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_begin = nullptr;
+  std::vector<Sub> subs;
   std::vector<void *> allocs;
-  Workspace ws;  // device pointers of the internal workspace
   // device staging for the host API
   int *d_mode = nullptr;
   double *d_x0 = nullptr, *d_pref = nullptr, *d_vref = nullptr, *d_xreg = nullptr, *d_tauref = nullptr, *d_xsinit = nullptr,
@@ -62,12 +73,14 @@ struct ffmpc_handle {
   int *o_iters = nullptr, *o_ok = nullptr;
   // receding-horizon tick state (ffmpc_tick_batch)
   TickState tick = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int tick_B = -1;          // batch size of the stored plans
+  bool plan_dirty = true;   // a solve since the last tick overwrote the workspace the plans live in
   double *d_taubias = nullptr, *o_taucmd = nullptr, *o_tauraw = nullptr, *o_fnpred = nullptr;
   int *o_unstable = nullptr;
   double last_ms = 0.0;
   int last_launches = 0;
   bool timing_valid = false;
-  // per-kernel-family profiling (ffmpc_set_profiling / ffmpc_get_profile)
+  // per-kernel-family profiling (ffmpc_set_profiling / ffmpc_get_profile): sub-batches then run one after another on the main stream
   bool profiling = false;
   std::vector<cudaEvent_t> pev;      // event pool
   std::vector<int> pfam;             // family of the interval that ENDS at event i+1
@@ -99,7 +112,7 @@ int check_cfg(const ffmpc_config *c) {
 }
 
 // profiling: an event after every kernel family; the interval that ends at it is attributed to `fam`
-int mark(ffmpc_handle *h, int fam, int nlaunch) {
+int mark(ffmpc_handle *h, cudaStream_t st, int fam, int nlaunch) {
   if (!h->profiling) return FFMPC_OK;
   if (h->pn >= (int)h->pev.size()) {
     cudaEvent_t e;
@@ -109,23 +122,56 @@ int mark(ffmpc_handle *h, int fam, int nlaunch) {
   }
   h->pfam[h->pn] = fam;
   if (fam >= 0) h->fam_launches[fam] += nlaunch;
-  CU(cudaEventRecord(h->pev[h->pn], h->stream));
+  CU(cudaEventRecord(h->pev[h->pn], st));
   h->pn++;
   return FFMPC_OK;
 }
 
-int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
+// contiguous sub-batches of a batch of B instances: one if it fits a sub-batch workspace, else balanced over the streams
+std::vector<Chunk> plan_chunks(const ffmpc_handle *h, size_t B) {
+  std::vector<Chunk> c;
+  const size_t S = h->subs.size();
+  if (B <= (size_t)h->cap || S == 1) {
+    c.push_back({0, B});
+    return c;
+  }
+  const size_t per = (B + S - 1) / S;
+  for (size_t off = 0; off < B; off += per) c.push_back({off, std::min(per, B - off)});
+  return c;
+}
+
+void bind_chunk(Workspace &ws, const ffmpc_batch_in *in, const Chunk &ck, int max_iters, int fixed_iters) {
+  const size_t o = ck.off, N = (size_t)ws.N, nx = (size_t)ws.nx;
+  ws.B = (int)ck.cnt;
+  ws.max_iters = max_iters;
+  ws.fixed_iters = fixed_iters;
+  ws.mode = in->mode + o;
+  ws.x0 = in->x0 + o * nx;
+  ws.p_ref = in->p_ref + o * (N + 1) * 3;
+  ws.v_ref = in->v_ref + o * (N + 1) * 3;
+  ws.x_reg_ref = in->x_reg_ref + o * 14;
+  ws.tau_ref_in = in->tau_ref ? in->tau_ref + o * NJ : nullptr;
+  ws.xs_init = in->xs_init ? in->xs_init + o * (N + 1) * nx : nullptr;
+  ws.us_init = in->us_init ? in->us_init + o * N * NJ : nullptr;
+}
+
+int check_in(const ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters) {
+  if (!in) return fail(FFMPC_ERR_ARG, "null batch_in");
+  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
+  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
+  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
+  if (max_iters < 0) return fail(FFMPC_ERR_ARG, "max_iters must be >= 0");
+  return FFMPC_OK;
+}
+
+// the launch sequence of one sub-batch solve on stream `st` (ws already bound)
+int launch_solve(ffmpc_handle *h, const Workspace &wsb, cudaStream_t st, int max_iters, int &launches) {
   Params P;
   P.mdl = h->mdl;
   P.cfg = h->cfg;
-  P.ws = h->ws;
+  P.ws = wsb;
   const Workspace &ws = P.ws;
   const int B = ws.B, N = ws.N;
-  cudaStream_t st = h->stream;
-  launches = 0;
-  h->pn = 0;
-  for (int f = 0; f < FFMPC_NFAM; ++f) { h->fam_ms[f] = 0.0; h->fam_launches[f] = 0; }
-  if (int e = mark(h, -1, 0)) return e;
   FFMPC_LAUNCH(k_build_perm, 1, 1024, 1025 * sizeof(int), st, ws);
   FFMPC_LAUNCH(k_init_state, (B + 127) / 128, 128, 0, st, P);
   {
@@ -134,60 +180,91 @@ int launch_solve(ffmpc_handle *h, int max_iters, int &launches) {
     FFMPC_LAUNCH(k_init_traj, grid, 256, 0, st, ws);
   }
   launches += 3;
-  if (int e = mark(h, FFMPC_FAM_OTHER, 3)) return e;
+  if (int e = mark(h, st, FFMPC_FAM_OTHER, 3)) return e;
   for (int it = 0; it < max_iters; ++it) {
 #ifdef FFMPC_EMU
-    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: node_diff\n", it);
+    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d\n", it);
 #endif
     launch_node_diff_coop(P, st);
-    if (int e = mark(h, FFMPC_FAM_NODE_DIFF, 2)) return e;
-#ifdef FFMPC_EMU
-    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: backward\n", it);
-#endif
+    if (int e = mark(h, st, FFMPC_FAM_NODE_DIFF, 2)) return e;
     launch_backward(P, st);
-    if (int e = mark(h, FFMPC_FAM_BACKWARD, 1)) return e;
-#ifdef FFMPC_EMU
-    if (getenv("FFMPC_TRACE")) fprintf(stderr, "[emu] iteration %d: forward\n", it);
-#endif
+    if (int e = mark(h, st, FFMPC_FAM_BACKWARD, 1)) return e;
     const int nfwd = launch_forward_coop(P, it, st);
-    if (int e = mark(h, FFMPC_FAM_FORWARD, nfwd)) return e;
+    if (int e = mark(h, st, FFMPC_FAM_FORWARD, nfwd)) return e;
     launches += 3 + nfwd;
   }
   CU(cudaGetLastError());
   return FFMPC_OK;
 }
 
-int launch_export(ffmpc_handle *h, const ffmpc_batch_out *out, int &launches) {
+int launch_export(ffmpc_handle *h, const Workspace &ws, cudaStream_t st, const ffmpc_batch_out *out, size_t off, int &launches) {
+  const size_t N = (size_t)ws.N, nx = (size_t)ws.nx;
   ExportPtrs o;
-  o.xs = out->xs; o.us = out->us; o.K = out->K; o.k = out->k; o.cost = out->cost; o.stop = out->stop;
-  o.gaps = out->gaps; o.f_pred = out->f_pred; o.iters = out->iters; o.ok = out->ok;
-  const size_t total = (size_t)h->ws.B * h->ws.N * NJ * h->ws.nx;
+  o.xs = out->xs ? out->xs + off * (N + 1) * nx : nullptr;
+  o.us = out->us ? out->us + off * N * NJ : nullptr;
+  o.K = out->K ? out->K + off * N * NJ * nx : nullptr;
+  o.k = out->k ? out->k + off * N * NJ : nullptr;
+  o.cost = out->cost ? out->cost + off : nullptr;
+  o.stop = out->stop ? out->stop + off : nullptr;
+  o.gaps = out->gaps ? out->gaps + off * (N + 1) * nx : nullptr;
+  o.f_pred = out->f_pred ? out->f_pred + off * 6 : nullptr;
+  o.iters = out->iters ? out->iters + off : nullptr;
+  o.ok = out->ok ? out->ok + off : nullptr;
+  const size_t total = (size_t)ws.B * N * NJ * nx;
   const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
-  FFMPC_LAUNCH(k_export, grid, 256, 0, h->stream, h->ws, o);
+  FFMPC_LAUNCH(k_export, grid, 256, 0, st, ws, o);
   launches += 1;
-  if (int e = mark(h, FFMPC_FAM_OTHER, 1)) return e;
+  if (int e = mark(h, st, FFMPC_FAM_OTHER, 1)) return e;
   CU(cudaGetLastError());
   return FFMPC_OK;
 }
 
-int bind_inputs(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters) {
-  if (!in) return fail(FFMPC_ERR_ARG, "null batch_in");
-  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
-  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
-  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
-  if (max_iters < 0) return fail(FFMPC_ERR_ARG, "max_iters must be >= 0");
-  Workspace &ws = h->ws;
-  ws.B = in->B;
-  ws.max_iters = max_iters;
-  ws.fixed_iters = fixed_iters;
-  ws.mode = in->mode;
-  ws.x0 = in->x0;
-  ws.p_ref = in->p_ref;
-  ws.v_ref = in->v_ref;
-  ws.x_reg_ref = in->x_reg_ref;
-  ws.tau_ref_in = in->tau_ref;
-  ws.xs_init = in->xs_init;
-  ws.us_init = in->us_init;
+void reset_profile(ffmpc_handle *h) {
+  h->pn = 0;
+  for (int f = 0; f < FFMPC_NFAM; ++f) { h->fam_ms[f] = 0.0; h->fam_launches[f] = 0; }
+}
+
+// stream a sub-batch runs on: its own, or the caller's / main stream when there is nothing to overlap (one sub-batch)
+// or when per-family profiling needs a serial timeline
+cudaStream_t sub_stream(ffmpc_handle *h, size_t c, size_t nchunks, cudaStream_t base) {
+  return (nchunks == 1 || h->profiling) ? base : h->subs[c].stream;
+}
+
+int alloc_workspace(ffmpc_handle *h, Workspace &ws, size_t B) {
+  const size_t N = (size_t)h->N, nx = (size_t)h->nx;
+  const ffmpc_config *cfg = &h->cfg;
+  std::memset(&ws, 0, sizeof(ws));
+  ws.N = h->N;
+  ws.nx = h->nx;
+  // line search: accepted + one trial slot (queue mode: one launch per step length over the compacted queue of rejected
+  // instances); small batches roll every step length out at once (speculative mode: one trial slot per step length)
+  ws.nslots = 2;
+  ws.spec = (h->opt.line_search == FFMPC_LS_SPECULATIVE || (h->opt.line_search == FFMPC_LS_AUTO && h->max_batch <= 512)) ? 1 : 0;
+  if (ws.spec) ws.nslots = 1 + cfg->n_alphas;
+  int rc = FFMPC_OK;
+#define DA(ptr, count) if (rc == FFMPC_OK) rc = dalloc(h, &(ptr), (count))
+  DA(ws.tau_ref, B * NJ);
+  DA(ws.perm, B);
+  DA(ws.counts, 2);
+  DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
+  DA(ws.us, (size_t)ws.nslots * B * N * NJ);
+  DA(ws.fs, B * (N + 1) * nx);
+  DA(ws.rec, B * (N + 1) * REC_SIZE);
+  DA(ws.ncost, B * (N + 1));
+  DA(ws.K, B * N * NJ * nx);
+  DA(ws.k, B * N * NJ);
+  DA(ws.Vfs, B * (N + 1) * nx);
+  DA(ws.preg, B); DA(ws.cost, B); DA(ws.dg, B); DA(ws.dq, B); DA(ws.stop, B); DA(ws.d1, B); DA(ws.d2, B);
+  DA(ws.feas, B); DA(ws.wasfeas, B); DA(ws.recalc, B); DA(ws.done, B); DA(ws.ok, B); DA(ws.iter, B); DA(ws.cur, B);
+  DA(ws.cost_valid, B);
+  DA(ws.f_pred, B * 6);
+  DA(ws.queue, 4 * B);
+  DA(ws.qcount, 64);
+  DA(ws.trial, ws.spec ? B * (size_t)cfg->n_alphas * 10 : 1);
+#undef DA
+  if (rc != FFMPC_OK) return rc;
+  // the padding entries of the knot records are never written again (ffmpc_math.cuh: record layout)
+  CU(cudaMemset(ws.rec, 0, B * (N + 1) * REC_SIZE * sizeof(double)));
   return FFMPC_OK;
 }
 
@@ -244,7 +321,7 @@ void ffmpc_default_config(ffmpc_config *c, int variant) {
 void ffmpc_default_options(ffmpc_options *o) {
   std::memset(o, 0, sizeof(*o));
   o->line_search = FFMPC_LS_AUTO;
-  o->host_chunks = 0;
+  o->sub_batches = 0;
 }
 
 int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch, ffmpc_handle **out) {
@@ -267,7 +344,7 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
   ffmpc_default_options(&o);
   if (opt) o = *opt;
   if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_SPECULATIVE) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
-  if (o.host_chunks < 0 || o.host_chunks > 64) return fail(FFMPC_ERR_ARG, "options.host_chunks out of range (0 = auto, 1 .. 64)");
+  if (o.sub_batches < 0 || o.sub_batches > FFMPC_MAX_SUB_BATCHES) return fail(FFMPC_ERR_ARG, "options.sub_batches out of range (0 = auto, 1 .. 16)");
   ffmpc_handle *h = new ffmpc_handle();
   h->opt = o;
   h->device = device;
@@ -276,47 +353,34 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
   h->mdl = *model;
   h->N = cfg->horizon;
   h->nx = cfg->variant == FFMPC_VARIANT_FF ? 21 : 14;
-  const size_t B = (size_t)max_batch, N = (size_t)h->N, nx = (size_t)h->nx;
-  Workspace &ws = h->ws;
-  std::memset(&ws, 0, sizeof(ws));
-  ws.N = h->N;
-  ws.nx = h->nx;
+  // sub-batches, auto: measured on B200 (profiles/r2d_*): device throughput is flat in the split at 65536 instances and
+  // gains 3-7 % at 8192 / 16384 (kernel tails and late line-search passes overlap), the host API gains 10-16 % (result
+  // copies overlap the other sub-batches' solves); below 4096 instances one stream, and the speculative line search of
+  // small handles wants the whole batch in one launch
+  int S = o.sub_batches;
+  if (S == 0) S = max_batch < 4096 ? 1 : (max_batch < 16384 ? 2 : 4);
+  S = std::max(1, std::min(S, max_batch));
+  h->opt.sub_batches = S;
+  h->cap = (max_batch + S - 1) / S;
   int rc = FFMPC_OK;
-#define DA(ptr, count) if (rc == FFMPC_OK) rc = dalloc(h, &(ptr), (count))
   if (cudaStreamCreate(&h->stream) != cudaSuccess) rc = fail(FFMPC_ERR_CUDA, "cudaStreamCreate failed");
-  if (rc == FFMPC_OK && (cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess)) rc = fail(FFMPC_ERR_CUDA, "cudaEventCreate failed");
-  DA(ws.tau_ref, B * NJ);
-  DA(ws.perm, B);
-  DA(ws.counts, 2);
-  // line search: accepted + one trial slot (queue mode: one launch per step length over the compacted queue of rejected
-  // instances); small batches roll every step length out at once (speculative mode: one trial slot per step length)
-  ws.nslots = 2;
-  ws.spec = (h->opt.line_search == FFMPC_LS_SPECULATIVE || (h->opt.line_search == FFMPC_LS_AUTO && max_batch <= 512)) ? 1 : 0;
-  if (ws.spec) ws.nslots = 1 + cfg->n_alphas;
-  DA(ws.xs, (size_t)ws.nslots * B * (N + 1) * nx);
-  DA(ws.us, (size_t)ws.nslots * B * N * NJ);
-  DA(ws.fs, B * (N + 1) * nx);
-  DA(ws.rec, B * (N + 1) * REC_SIZE);
-  DA(ws.ncost, B * (N + 1));
-  DA(ws.K, B * N * NJ * nx);
-  DA(ws.k, B * N * NJ);
-  DA(ws.Vfs, B * (N + 1) * nx);
-  DA(ws.preg, B); DA(ws.cost, B); DA(ws.dg, B); DA(ws.dq, B); DA(ws.stop, B); DA(ws.d1, B); DA(ws.d2, B);
-  DA(ws.feas, B); DA(ws.wasfeas, B); DA(ws.recalc, B); DA(ws.done, B); DA(ws.ok, B); DA(ws.iter, B); DA(ws.cur, B);
-  DA(ws.cost_valid, B);
-  DA(ws.f_pred, B * 6);
-  DA(ws.queue, 4 * B);
-  DA(ws.qcount, 64);
-  DA(ws.trial, ws.spec ? B * (size_t)cfg->n_alphas * 10 : 1);
-#undef DA
+  if (rc == FFMPC_OK && (cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
+                         cudaEventCreateWithFlags(&h->ev_begin, cudaEventDisableTiming) != cudaSuccess))
+    rc = fail(FFMPC_ERR_CUDA, "cudaEventCreate failed");
+  int prio_least = 0, prio_greatest = 0;
+  if (rc == FFMPC_OK && cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest) != cudaSuccess) { prio_least = prio_greatest = 0; }
+  h->subs.resize(S);
+  for (int c = 0; c < S && rc == FFMPC_OK; ++c) {
+    Sub &sb = h->subs[c];
+    const int prio = std::min(prio_least, prio_greatest + c);  // numerically lower = more urgent: the first sub-batch runs first
+    if (cudaStreamCreateWithPriority(&sb.stream, cudaStreamNonBlocking, prio) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sb.done, cudaEventDisableTiming) != cudaSuccess)
+      rc = fail(FFMPC_ERR_CUDA, "sub-batch stream / event creation failed");
+    if (rc == FFMPC_OK) rc = alloc_workspace(h, sb.ws, (size_t)h->cap);
+  }
   if (rc != FFMPC_OK) {
     ffmpc_destroy(h);
     return rc;
-  }
-  // the padding entries of the knot records are never written again (ffmpc_math.cuh: record layout)
-  if (cudaMemset(ws.rec, 0, B * (N + 1) * REC_SIZE * sizeof(double)) != cudaSuccess) {
-    ffmpc_destroy(h);
-    return fail(FFMPC_ERR_CUDA, "cudaMemset(records) failed");
   }
   if (prepare_backward() != 0 || prepare_coop_node() != 0 || prepare_coop_fwd() != 0) {
     ffmpc_destroy(h);
@@ -329,39 +393,58 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
 void ffmpc_destroy(ffmpc_handle *h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
   for (void *p : h->allocs) cudaFree(p);
   for (cudaEvent_t e : h->pev) cudaEventDestroy(e);
+  for (Sub &sb : h->subs) {
+    if (sb.done) cudaEventDestroy(sb.done);
+    if (sb.stream) cudaStreamDestroy(sb.stream);
+  }
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
-  if (h->ev_chunk) cudaEventDestroy(h->ev_chunk);
-  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->ev_begin) cudaEventDestroy(h->ev_begin);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
 
+// Device pointers.  Work is enqueued behind everything already on `stream` (NULL: the handle's own stream), and `stream`
+// continues only after every sub-batch has finished: the call is stream-ordered for the caller, as a single launch would be.
 int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters, const ffmpc_batch_out *out,
                       void *stream) {
   if (!h || !out) return fail(FFMPC_ERR_ARG, "null handle / out");
   CU(cudaSetDevice(h->device));
-  if (int e = bind_inputs(h, in, max_iters, fixed_iters)) return e;
-  cudaStream_t saved = h->stream;
-  if (stream) h->stream = (cudaStream_t)stream;
-  int launches = 0, l2 = 0;
-  int rc = launch_solve(h, max_iters, launches);
-  if (rc == FFMPC_OK) rc = launch_export(h, out, l2);
-  h->stream = saved;
-  h->last_launches = launches + l2;
+  if (int e = check_in(h, in, max_iters)) return e;
+  cudaStream_t base = stream ? (cudaStream_t)stream : h->stream;
+  const std::vector<Chunk> chunks = plan_chunks(h, (size_t)in->B);
+  const bool fan = chunks.size() > 1 && !h->profiling;
+  reset_profile(h);
+  if (int e = mark(h, base, -1, 0)) return e;
+  if (fan) CU(cudaEventRecord(h->ev_begin, base));
+  int launches = 0;
+  for (size_t c = 0; c < chunks.size(); ++c) {
+    Sub &sb = h->subs[c];
+    cudaStream_t st = sub_stream(h, c, chunks.size(), base);
+    if (fan) CU(cudaStreamWaitEvent(st, h->ev_begin, 0));
+    bind_chunk(sb.ws, in, chunks[c], max_iters, fixed_iters);
+    int rc = launch_solve(h, sb.ws, st, max_iters, launches);
+    if (rc == FFMPC_OK) rc = launch_export(h, sb.ws, st, out, chunks[c].off, launches);
+    if (rc != FFMPC_OK) return rc;
+    if (fan) {
+      CU(cudaEventRecord(sb.done, st));
+      CU(cudaStreamWaitEvent(base, sb.done, 0));
+    }
+  }
+  h->plan_dirty = true;
+  h->last_launches = launches;
   h->timing_valid = false;
-  return rc;
+  return FFMPC_OK;
 }
 
 int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
                            const ffmpc_batch_out *out) {
   if (!h || !out || !in) return fail(FFMPC_ERR_ARG, "null handle / in / out");
   CU(cudaSetDevice(h->device));
-  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
-  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
-  if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
+  if (int e = check_in(h, in, max_iters)) return e;
   const size_t Bm = (size_t)h->max_batch, B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx;
   int rc = FFMPC_OK;
 #define DA(ptr, count) if (rc == FFMPC_OK && !(ptr)) rc = dalloc(h, &(ptr), (count))
@@ -381,76 +464,51 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
   if (out->ok) DA(h->o_ok, Bm);
 #undef DA
   if (rc != FFMPC_OK) return rc;
-  cudaStream_t st = h->stream;
-#define H2D(dst, src, count, T) CU(cudaMemcpyAsync((dst), (src), (count) * sizeof(T), cudaMemcpyHostToDevice, st))
-  H2D(h->d_mode, in->mode, B, int);
-  H2D(h->d_x0, in->x0, B * nx, double);
-  H2D(h->d_pref, in->p_ref, B * (N + 1) * 3, double);
-  H2D(h->d_vref, in->v_ref, B * (N + 1) * 3, double);
-  H2D(h->d_xreg, in->x_reg_ref, B * 14, double);
-  if (in->tau_ref) H2D(h->d_tauref, in->tau_ref, B * NJ, double);
-  if (in->xs_init) H2D(h->d_xsinit, in->xs_init, B * (N + 1) * nx, double);
-  if (in->us_init) H2D(h->d_usinit, in->us_init, B * N * NJ, double);
-#undef H2D
-  // Large batches are solved in chunks: a chunk's results (K alone is 73 KB per instance) travel to the host on a second
-  // stream while the next chunk is solved, so most of the device->host time hides behind compute.  options.host_chunks:
-  // 1 = unsplit, k > 1 = k equal chunks, 0 (auto) = a leading 7/8 and a trailing 1/8 for batches of >= 16384 instances (the
-  // trailing solve about equals the leading chunk's copy time on PCIe gen5).  Same kernels, same per-instance arithmetic:
-  // results do not depend on the split.
-  std::vector<size_t> chunks;
-  {
-    const int k = h->profiling ? 1 : h->opt.host_chunks;
-    if (k == 0 && B >= 16384) {
-      size_t tail = ((B / 8 + 511) / 512) * 512;
-      tail = std::min(std::max<size_t>(tail, 1), B - 1);
-      chunks = {B - tail, tail};
-    } else if (k > 1 && B >= (size_t)k) {
-      const size_t per = (B + k - 1) / k;
-      for (size_t off = 0; off < B; off += per) chunks.push_back(std::min(per, B - off));
-    } else {
-      chunks = {B};
-    }
-  }
-  const bool split = chunks.size() > 1;
-  if (split && !h->copy_stream) {
-    if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&h->ev_chunk, cudaEventDisableTiming) != cudaSuccess)
-      return fail(FFMPC_ERR_CUDA, "copy stream / event creation failed");
-  }
+  // device-side views of the caller's host buffers
+  ffmpc_batch_in din;
+  din.B = in->B;
+  din.mode = h->d_mode; din.x0 = h->d_x0; din.p_ref = h->d_pref; din.v_ref = h->d_vref; din.x_reg_ref = h->d_xreg;
+  din.tau_ref = in->tau_ref ? h->d_tauref : nullptr;
+  din.xs_init = in->xs_init ? h->d_xsinit : nullptr;
+  din.us_init = in->us_init ? h->d_usinit : nullptr;
+  ffmpc_batch_out dout;
+  dout.xs = out->xs ? h->o_xs : nullptr; dout.us = out->us ? h->o_us : nullptr; dout.K = out->K ? h->o_K : nullptr;
+  dout.k = out->k ? h->o_k : nullptr; dout.cost = out->cost ? h->o_cost : nullptr; dout.stop = out->stop ? h->o_stop : nullptr;
+  dout.gaps = out->gaps ? h->o_gaps : nullptr; dout.f_pred = out->f_pred ? h->o_fpred : nullptr;
+  dout.iters = out->iters ? h->o_iters : nullptr; dout.ok = out->ok ? h->o_ok : nullptr;
+  const std::vector<Chunk> chunks = plan_chunks(h, B);
+  const bool fan = chunks.size() > 1 && !h->profiling;
+  reset_profile(h);
+  // Each sub-batch is a pipeline of its own on its own stream: inputs in, solve, export, results out.  A finished
+  // sub-batch's device->host copies (K alone is 73 KB per instance) overlap the solves of the others; pass pinned host
+  // buffers to get asynchronous copies.
+  CU(cudaEventRecord(h->ev0, h->stream));
   int launches = 0;
-  CU(cudaEventRecord(h->ev0, st));
-  size_t off = 0;
   for (size_t c = 0; c < chunks.size(); ++c) {
-    const size_t cnt = chunks[c];
-    ffmpc_batch_in din;
-    din.B = (int)cnt;
-    din.mode = h->d_mode + off; din.x0 = h->d_x0 + off * nx; din.p_ref = h->d_pref + off * (N + 1) * 3;
-    din.v_ref = h->d_vref + off * (N + 1) * 3; din.x_reg_ref = h->d_xreg + off * 14;
-    din.tau_ref = in->tau_ref ? h->d_tauref + off * NJ : nullptr;
-    din.xs_init = in->xs_init ? h->d_xsinit + off * (N + 1) * nx : nullptr;
-    din.us_init = in->us_init ? h->d_usinit + off * N * NJ : nullptr;
-    ffmpc_batch_out dout;
-    dout.xs = out->xs ? h->o_xs + off * (N + 1) * nx : nullptr; dout.us = out->us ? h->o_us + off * N * NJ : nullptr;
-    dout.K = out->K ? h->o_K + off * N * NJ * nx : nullptr; dout.k = out->k ? h->o_k + off * N * NJ : nullptr;
-    dout.cost = out->cost ? h->o_cost + off : nullptr; dout.stop = out->stop ? h->o_stop + off : nullptr;
-    dout.gaps = out->gaps ? h->o_gaps + off * (N + 1) * nx : nullptr; dout.f_pred = out->f_pred ? h->o_fpred + off * 6 : nullptr;
-    dout.iters = out->iters ? h->o_iters + off : nullptr; dout.ok = out->ok ? h->o_ok + off : nullptr;
-    if (int e = bind_inputs(h, &din, max_iters, fixed_iters)) return e;
-    int l1 = 0, l2 = 0;
-    rc = launch_solve(h, max_iters, l1);
-    if (rc == FFMPC_OK) rc = launch_export(h, &dout, l2);
+    Sub &sb = h->subs[c];
+    cudaStream_t st = sub_stream(h, c, chunks.size(), h->stream);
+    const size_t off = chunks[c].off, cnt = chunks[c].cnt;
+    if (fan) CU(cudaStreamWaitEvent(st, h->ev0, 0));
+#define H2D(dst, src, per, T) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyHostToDevice, st))
+    H2D(h->d_mode, in->mode, 1, int);
+    H2D(h->d_x0, in->x0, nx, double);
+    H2D(h->d_pref, in->p_ref, (N + 1) * 3, double);
+    H2D(h->d_vref, in->v_ref, (N + 1) * 3, double);
+    H2D(h->d_xreg, in->x_reg_ref, 14, double);
+    if (in->tau_ref) H2D(h->d_tauref, in->tau_ref, NJ, double);
+    if (in->xs_init) H2D(h->d_xsinit, in->xs_init, (N + 1) * nx, double);
+    if (in->us_init) H2D(h->d_usinit, in->us_init, N * NJ, double);
+#undef H2D
+    if (c == 0) { if (int e = mark(h, st, -1, 0)) return e; }
+    bind_chunk(sb.ws, &din, chunks[c], max_iters, fixed_iters);
+    rc = launch_solve(h, sb.ws, st, max_iters, launches);
+    if (rc == FFMPC_OK) rc = launch_export(h, sb.ws, st, &dout, off, launches);
     if (rc != FFMPC_OK) return rc;
-    launches += l1 + l2;
-    const bool last = (c + 1 == chunks.size());
-    cudaStream_t cs = st;
-    if (last) {
-      CU(cudaEventRecord(h->ev1, st));
-    } else {
-      // the copy stream takes this chunk's results as soon as its export is done; the solve stream goes on with the next chunk
-      CU(cudaEventRecord(h->ev_chunk, st));
-      CU(cudaStreamWaitEvent(h->copy_stream, h->ev_chunk, 0));
-      cs = h->copy_stream;
+    if (fan) {
+      CU(cudaEventRecord(sb.done, st));
+      CU(cudaStreamWaitEvent(h->stream, sb.done, 0));
     }
-#define D2H(dst, src, per, T) if (dst) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyDeviceToHost, cs))
+#define D2H(dst, src, per, T) if (dst) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyDeviceToHost, st))
     D2H(out->xs, h->o_xs, (N + 1) * nx, double);
     D2H(out->us, h->o_us, N * NJ, double);
     D2H(out->K, h->o_K, N * NJ * nx, double);
@@ -462,12 +520,15 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
     D2H(out->iters, h->o_iters, 1, int);
     D2H(out->ok, h->o_ok, 1, int);
 #undef D2H
-    off += cnt;
   }
-  if (split) CU(cudaStreamSynchronize(h->copy_stream));
-  CU(cudaStreamSynchronize(st));
+  // ev1 on the main stream: behind the last kernel of every sub-batch (single stream: behind its copies as well)
+  CU(cudaEventRecord(h->ev1, h->stream));
+  if (fan)
+    for (size_t c = 0; c < chunks.size(); ++c) CU(cudaStreamSynchronize(h->subs[c].stream));
+  CU(cudaStreamSynchronize(h->stream));
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  h->plan_dirty = true;
   h->last_ms = ms;
   h->last_launches = launches;
   h->timing_valid = true;
@@ -485,7 +546,7 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
     if (inst[m] < 0 || inst[m] >= in->B || knot[m] < 0 || knot[m] > h->N) return fail(FFMPC_ERR_ARG, "inst / knot out of range");
   const size_t B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx, Ms = (size_t)M;
   cudaStream_t st = h->stream;
-  // transient device buffers (test hook, not a hot path)
+  // transient device buffers (test hook, not a hot path); nothing of the solver workspace is touched
   std::vector<void *> tmp;
   auto talloc = [&](size_t bytes) -> void * {
     void *p = nullptr;
@@ -499,16 +560,16 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
     if (p) cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, st);
     return p;
   };
-  ffmpc_batch_in din;
-  din.B = in->B;
-  din.mode = (const int *)up(in->mode, B * sizeof(int));
-  din.x0 = (const double *)up(in->x0, B * nx * 8);
-  din.p_ref = (const double *)up(in->p_ref, B * (N + 1) * 24);
-  din.v_ref = (const double *)up(in->v_ref, B * (N + 1) * 24);
-  din.x_reg_ref = (const double *)up(in->x_reg_ref, B * 14 * 8);
-  din.tau_ref = in->tau_ref ? (const double *)up(in->tau_ref, B * NJ * 8) : nullptr;
-  din.xs_init = nullptr;
-  din.us_init = nullptr;
+  Workspace ws;
+  std::memset(&ws, 0, sizeof(ws));
+  ws.B = in->B; ws.N = h->N; ws.nx = h->nx;
+  ws.mode = (const int *)up(in->mode, B * sizeof(int));
+  ws.x0 = (const double *)up(in->x0, B * nx * 8);
+  ws.p_ref = (const double *)up(in->p_ref, B * (N + 1) * 24);
+  ws.v_ref = (const double *)up(in->v_ref, B * (N + 1) * 24);
+  ws.x_reg_ref = (const double *)up(in->x_reg_ref, B * 14 * 8);
+  ws.tau_ref_in = in->tau_ref ? (const double *)up(in->tau_ref, B * NJ * 8) : nullptr;
+  ws.tau_ref = (double *)talloc(B * NJ * 8);
   NodeEvalArgs A;
   A.M = M;
   A.inst = (const int *)up(inst, Ms * sizeof(int));
@@ -523,13 +584,11 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
   if (d_rec) cudaMemsetAsync(d_rec, 0, Ms * REC_SIZE * 8, st);
   for (void *p : tmp)
     if (!p) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
-  if (!din.mode || !A.Luu || !d_rec) { cleanup(); return fail(FFMPC_ERR_CUDA, "cudaMalloc failed in node_eval"); }
-  if (int e = bind_inputs(h, &din, 0, 1)) { cleanup(); return e; }
   Params P;
   P.mdl = h->mdl;
   P.cfg = h->cfg;
-  P.ws = h->ws;
-  FFMPC_LAUNCH(k_init_state, (in->B + 127) / 128, 128, 0, st, P);  // resolves tau_ref
+  P.ws = ws;
+  FFMPC_LAUNCH(k_resolve_tau_ref, (in->B + 127) / 128, 128, 0, st, P);
   launch_node_eval_coop(P, A, d_rec, st);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess) { cleanup(); return fail(FFMPC_ERR_CUDA, std::string("node_eval launch: ") + cudaGetErrorString(le)); }
@@ -566,42 +625,68 @@ int ffmpc_tick_batch(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_
                      const ffmpc_tick_out *out, void *stream) {
   if (!h || !in || !pol || !out) return fail(FFMPC_ERR_ARG, "null handle / in / policy / out");
   CU(cudaSetDevice(h->device));
+  if (in->B < 1) return fail(FFMPC_ERR_ARG, "batch size must be >= 1");
+  if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
   if (!in->mode || !in->x_now || !in->p_ref || !in->v_ref || !in->x_reg_ref || !in->tau_bias)
     return fail(FFMPC_ERR_ARG, "mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias are required");
   if (!(pol->dt_mpc > 0.0)) return fail(FFMPC_ERR_ARG, "policy.dt_mpc must be > 0");
+  if (max_iters < 0) return fail(FFMPC_ERR_ARG, "max_iters must be >= 0");
   if (int e = tick_state(h)) return e;
-  ffmpc_batch_in bin;
-  bin.B = in->B; bin.mode = in->mode; bin.x0 = in->x_now; bin.p_ref = in->p_ref; bin.v_ref = in->v_ref; bin.x_reg_ref = in->x_reg_ref;
-  bin.tau_ref = nullptr; bin.xs_init = h->tick.xs_init; bin.us_init = h->tick.us_init;
-  if (int e = bind_inputs(h, &bin, max_iters, fixed_iters)) return e;
-  cudaStream_t saved = h->stream;
-  if (stream) h->stream = (cudaStream_t)stream;
-  cudaStream_t st = h->stream;
-  TickArgs A;
-  A.st = h->tick; A.reset = in->reset; A.mode = in->mode; A.x_now = in->x_now; A.tau_bias = in->tau_bias; A.pol = *pol;
-  A.tau_cmd = out->tau_cmd; A.tau_raw = out->tau_raw; A.cost = out->cost; A.fn_pred = out->fn_pred;
-  A.iters = out->iters; A.ok = out->ok; A.unstable = out->unstable;
-  Params P;
-  P.mdl = h->mdl; P.cfg = h->cfg; P.ws = h->ws;
-  const size_t total = (size_t)h->ws.B * (h->N + 1) * h->nx;
-  const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
-  FFMPC_LAUNCH(k_tick_prepare, grid, 256, 0, st, h->ws, A);
-  int launches = 0, l2 = 0;
-  int rc = launch_solve(h, max_iters, launches);
-  if (rc == FFMPC_OK) {
-    FFMPC_LAUNCH(k_tick_policy, (h->ws.B + 127) / 128, 128, 0, st, P, A);
+  // The plans of the previous tick ARE the workspace of its solve (instance b of sub-batch c).  They are unusable when the
+  // batch size changed (another instance -> sub-batch map) or when a solve ran on the handle in between: forget them.
+  const int reset = (in->reset || in->B != h->tick_B || h->plan_dirty) ? 1 : 0;
+  cudaStream_t base = stream ? (cudaStream_t)stream : h->stream;
+  const size_t N = (size_t)h->N, nx = (size_t)h->nx;
+  const std::vector<Chunk> chunks = plan_chunks(h, (size_t)in->B);
+  const bool fan = chunks.size() > 1 && !h->profiling;
+  reset_profile(h);
+  if (int e = mark(h, base, -1, 0)) return e;
+  if (fan) CU(cudaEventRecord(h->ev_begin, base));
+  int launches = 0;
+  for (size_t c = 0; c < chunks.size(); ++c) {
+    Sub &sb = h->subs[c];
+    cudaStream_t st = sub_stream(h, c, chunks.size(), base);
+    if (fan) CU(cudaStreamWaitEvent(st, h->ev_begin, 0));
+    const size_t o = chunks[c].off;
+    ffmpc_batch_in bin;
+    bin.B = in->B; bin.mode = in->mode; bin.x0 = in->x_now; bin.p_ref = in->p_ref; bin.v_ref = in->v_ref; bin.x_reg_ref = in->x_reg_ref;
+    bin.tau_ref = in->tau_ref; bin.xs_init = h->tick.xs_init; bin.us_init = h->tick.us_init;
+    bind_chunk(sb.ws, &bin, chunks[c], max_iters, fixed_iters);
+    TickArgs A;
+    A.st.plan_valid = h->tick.plan_valid + o; A.st.prev_mode = h->tick.prev_mode + o; A.st.tau_prev = h->tick.tau_prev + o * NJ;
+    A.st.xs_init = h->tick.xs_init + o * (N + 1) * nx; A.st.us_init = h->tick.us_init + o * N * NJ;
+    A.reset = reset; A.mode = in->mode + o; A.x_now = in->x_now + o * nx; A.tau_bias = in->tau_bias + o * NJ; A.pol = *pol;
+    A.tau_cmd = out->tau_cmd ? out->tau_cmd + o * NJ : nullptr; A.tau_raw = out->tau_raw ? out->tau_raw + o * NJ : nullptr;
+    A.cost = out->cost ? out->cost + o : nullptr; A.fn_pred = out->fn_pred ? out->fn_pred + o : nullptr;
+    A.iters = out->iters ? out->iters + o : nullptr; A.ok = out->ok ? out->ok + o : nullptr;
+    A.unstable = out->unstable ? out->unstable + o : nullptr;
+    Params P;
+    P.mdl = h->mdl; P.cfg = h->cfg; P.ws = sb.ws;
+    const size_t total = (size_t)sb.ws.B * (N + 1) * nx;
+    const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+    FFMPC_LAUNCH(k_tick_prepare, grid, 256, 0, st, sb.ws, A);
+    int rc = launch_solve(h, sb.ws, st, max_iters, launches);
+    if (rc != FFMPC_OK) return rc;
+    FFMPC_LAUNCH(k_tick_policy, (sb.ws.B + 127) / 128, 128, 0, st, P, A);
+    launches += 2;
     if (out->xs || out->us) {
       ffmpc_batch_out bo;
       std::memset(&bo, 0, sizeof(bo));
       bo.xs = out->xs; bo.us = out->us;
-      rc = launch_export(h, &bo, l2);
+      rc = launch_export(h, sb.ws, st, &bo, o, launches);
+      if (rc != FFMPC_OK) return rc;
+    }
+    if (cudaGetLastError() != cudaSuccess) return fail(FFMPC_ERR_CUDA, "tick kernel launch failed");
+    if (fan) {
+      CU(cudaEventRecord(sb.done, st));
+      CU(cudaStreamWaitEvent(base, sb.done, 0));
     }
   }
-  if (rc == FFMPC_OK && cudaGetLastError() != cudaSuccess) rc = fail(FFMPC_ERR_CUDA, "tick kernel launch failed");
-  h->stream = saved;
-  h->last_launches = launches + l2 + 2;
+  h->tick_B = in->B;
+  h->plan_dirty = false;
+  h->last_launches = launches;
   h->timing_valid = false;
-  return rc;
+  return FFMPC_OK;
 }
 
 int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_tick_policy *pol, int max_iters, int fixed_iters,
@@ -617,6 +702,7 @@ int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_
 #define DA(ptr, count) if (rc == FFMPC_OK && !(ptr)) rc = dalloc(h, &(ptr), (count))
   DA(h->d_mode, Bm); DA(h->d_x0, Bm * nx); DA(h->d_pref, Bm * (N + 1) * 3); DA(h->d_vref, Bm * (N + 1) * 3); DA(h->d_xreg, Bm * 14);
   DA(h->d_taubias, Bm * NJ);
+  if (in->tau_ref) DA(h->d_tauref, Bm * NJ);
   DA(h->o_taucmd, Bm * NJ); DA(h->o_tauraw, Bm * NJ); DA(h->o_fnpred, Bm); DA(h->o_cost, Bm); DA(h->o_iters, Bm); DA(h->o_ok, Bm);
   DA(h->o_unstable, Bm);
   if (out->xs) DA(h->o_xs, Bm * (N + 1) * nx);
@@ -631,9 +717,11 @@ int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_
   H2D(h->d_vref, in->v_ref, B * (N + 1) * 3, double);
   H2D(h->d_xreg, in->x_reg_ref, B * 14, double);
   H2D(h->d_taubias, in->tau_bias, B * NJ, double);
+  if (in->tau_ref) H2D(h->d_tauref, in->tau_ref, B * NJ, double);
 #undef H2D
   ffmpc_tick_in din = *in;
   din.mode = h->d_mode; din.x_now = h->d_x0; din.p_ref = h->d_pref; din.v_ref = h->d_vref; din.x_reg_ref = h->d_xreg; din.tau_bias = h->d_taubias;
+  din.tau_ref = in->tau_ref ? h->d_tauref : nullptr;
   ffmpc_tick_out dout;
   dout.tau_cmd = h->o_taucmd; dout.tau_raw = h->o_tauraw; dout.cost = h->o_cost; dout.fn_pred = h->o_fnpred;
   dout.iters = h->o_iters; dout.ok = h->o_ok; dout.unstable = h->o_unstable;
@@ -698,6 +786,16 @@ int ffmpc_sync(ffmpc_handle *h) {
   if (!h) return fail(FFMPC_ERR_ARG, "null handle");
   CU(cudaSetDevice(h->device));
   CU(cudaStreamSynchronize(h->stream));
+  for (Sub &sb : h->subs) CU(cudaStreamSynchronize(sb.stream));
+  return FFMPC_OK;
+}
+
+int ffmpc_get_info(ffmpc_handle *h, ffmpc_info *info) {
+  if (!h || !info) return fail(FFMPC_ERR_ARG, "null handle / info");
+  std::memset(info, 0, sizeof(*info));
+  info->sub_batches = (int)h->subs.size();
+  info->sub_batch_capacity = h->cap;
+  info->line_search = h->subs[0].ws.spec ? FFMPC_LS_SPECULATIVE : FFMPC_LS_QUEUE;
   return FFMPC_OK;
 }
 
@@ -705,9 +803,9 @@ const char *ffmpc_last_error(void) { return g_err.c_str(); }
 
 const char *ffmpc_version(void) {
 #ifdef FFMPC_EMU
-  return "ffmpc-b200 0.1 (CPU EMULATION TEST BUILD - not the product)";
+  return "ffmpc-b200 0.2 (CPU EMULATION TEST BUILD - not the product)";
 #else
-  return "ffmpc-b200 0.1 (sm_100a)";
+  return "ffmpc-b200 0.2 (sm_100a)";
 #endif
 }
 
@@ -721,6 +819,8 @@ void ffmpc_abi_sizes(int *sizes) {
   sizes[5] = (int)sizeof(ffmpc_tick_policy);
   sizes[6] = (int)sizeof(ffmpc_tick_in);
   sizes[7] = (int)sizeof(ffmpc_tick_out);
+  sizes[8] = (int)sizeof(ffmpc_options);
+  sizes[9] = (int)sizeof(ffmpc_info);
 }
 
 }  // extern "C"

@@ -120,6 +120,19 @@ static __global__ void k_build_perm(Workspace ws) {
   }
 }
 
+// tau_ref of instance b: the caller's, or g(q0) = RNEA(q0, 0, 0) (`_compute_tau_reference` "gravity_x0", crocoddyl_classical.py:447-460)
+FFMPC_DEV void resolve_tau_ref(const ffmpc_model &mdl, const Workspace &ws, int b) {
+  double tr[NJ];
+  if (ws.tau_ref_in) {
+    for (int i = 0; i < NJ; ++i) tr[i] = ws.tau_ref_in[b * NJ + i];
+  } else {
+    double q[NJ];
+    for (int i = 0; i < NJ; ++i) q[i] = ws.x0[(size_t)b * ws.nx + i];
+    gravity_torque(mdl, q, tr);
+  }
+  for (int i = 0; i < NJ; ++i) ws.tau_ref[b * NJ + i] = tr[i];
+}
+
 // per-instance solver state + tau_ref; thread per instance
 static __global__ void k_init_state(const __grid_constant__ Params P) {
   const Workspace &ws = P.ws;
@@ -137,15 +150,13 @@ static __global__ void k_init_state(const __grid_constant__ Params P) {
   ws.cur[b] = 0;
   ws.cost_valid[b] = 0;
   for (int i = 0; i < 6; ++i) ws.f_pred[b * 6 + i] = NAN;
-  double tr[NJ];
-  if (ws.tau_ref_in) {
-    for (int i = 0; i < NJ; ++i) tr[i] = ws.tau_ref_in[b * NJ + i];
-  } else {
-    double q[NJ];
-    for (int i = 0; i < NJ; ++i) q[i] = ws.x0[(size_t)b * ws.nx + i];
-    gravity_torque(P.mdl, q, tr);
-  }
-  for (int i = 0; i < NJ; ++i) ws.tau_ref[b * NJ + i] = tr[i];
+  resolve_tau_ref(P.mdl, ws, b);
+}
+
+// tau_ref alone (the knot-evaluation test hook needs nothing else of the per-instance state)
+static __global__ void k_resolve_tau_ref(const __grid_constant__ Params P) {
+  const int b = global_tid();
+  if (b < P.ws.B) resolve_tau_ref(P.mdl, P.ws, b);
 }
 
 // warm / cold start of xs, us (`_shift_guess` output is the caller's; NULL -> cold start) and k = 0

@@ -525,26 +525,30 @@ FFMPC_DEV bool riccati_sweep(const Params &P, int b, double *sm, double preg, bo
       qrow[0] = a0.x; qrow[1] = a0.y; qrow[2] = a1.x; qrow[3] = a1.y; qrow[4] = a2.x; qrow[5] = a2.y; qrow[6] = a3.x;
       qu = QS[64 + r7];
     }
-    __syncwarp();  // QS is rewritten with the inverse below
-    double hi[NJ], kv;
+    __syncwarp();  // QS is rewritten with L^-1 below
+    // Factor Quu = L L^T (BoxQP: of the free block, clamped rows / columns replaced by identity); the factor stays in LL / DI.
+    unsigned mask = 0x7fu;
+    double kv = 0.0, wv = 0.0;
     if (!box) {
-      // crocoddyl computeGains: Quu_llt.solve(Qxu^T), Quu_llt.solve(Qu) -- here through the explicit inverse (MMA operand)
-      if (!dist_masked_inverse(qrow, 0x7fu, 0.0, lane, LL, DI, hi)) { drain(); return false; }
-      double quv[NJ];
-      gather7(qu, quv);
-      kv = 0.0;
+      // crocoddyl computeGains: Quu_llt.solve(Qxu^T), Quu_llt.solve(Qu)
+      double a[NJ], dinv;
 #pragma unroll
-      for (int j = 0; j < NJ; ++j) kv += hi[j] * quv[j];
+      for (int j = 0; j < NJ; ++j) a[j] = qrow[j];
+      const bool okc = dist_chol7(a, 0x7fu, lane, dinv);
+      if (act7) {
+        sts_2(LL + lane * 8, a[0], a[1]); sts_2(LL + lane * 8 + 2, a[2], a[3]);
+        sts_2(LL + lane * 8 + 4, a[4], a[5]); sts_2(LL + lane * 8 + 6, a[6], 0.0);
+        DI[lane] = dinv;
+      }
+      __syncwarp();
+      if (!okc) { drain(); return false; }
     } else {
       const double lb = -cfg.tau_limits[r7] - u0_pre, ub = cfg.tau_limits[r7] - u0_pre;
       double xq = kq_pre;  // warm start = stored k_t (crocoddyl passes k_[t])
-      unsigned mask;
+      double hi[NJ];
       if (!dist_boxqp7(cfg, qrow, qu, lb, ub, xq, lane, LL, DI, mask, hi)) { drain(); return false; }
       kv = -xq;
       if (!((mask >> r7) & 1u)) qu = 0.0;  // clamped directions do not count for the stopping measure
-    }
-    double wv;
-    {
       double kvv[NJ], qk = 0.0;
       gather7(kv, kvv);
 #pragma unroll
@@ -552,45 +556,80 @@ FFMPC_DEV bool riccati_sweep(const Params &P, int b, double *sm, double preg, bo
       dgp += act7 ? qu * kv : 0.0;
       dqp -= act7 ? kv * qk : 0.0;
       wv = act7 ? qk - 2.0 * qu : 0.0;  // Quu k - 2 Qu
+      if (act7) kb[t * NJ + lane] = kv;
     }
-    if (lane < 8) {
-      double *h = HI + lane * 8;
-      const bool a7 = act7;
-      sts_2(h, a7 ? hi[0] : 0.0, a7 ? hi[1] : 0.0);
-      sts_2(h + 2, a7 ? hi[2] : 0.0, a7 ? hi[3] : 0.0);
-      sts_2(h + 4, a7 ? hi[4] : 0.0, a7 ? hi[5] : 0.0);
-      sts_2(h + 6, a7 ? hi[6] : 0.0, 0.0);
+    // Column `lane` of L^-1 by forward substitution (zero for a clamped index), stored transposed: HI[c * 8 + i] = Linv[i][c].
+    // The gains and the value update go through W = Qxu L^-T (K^T = W L^-1, Qxu K = W W^T): no product with the explicit
+    // inverse of an ill-conditioned Quu, and an exactly symmetric downdate.
+    {
+      double y[NJ];
+#pragma unroll
+      for (int i = 0; i < NJ; ++i) {
+        double sacc = (i == r7) ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k < i; ++k) sacc -= LL[i * 8 + k] * y[k];
+        y[i] = sacc * DI[i];
+      }
+      const bool keep = act7 && ((mask >> r7) & 1u);
+      if (lane < 8) {
+        double *h = HI + lane * 8;
+        sts_2(h, keep ? y[0] : 0.0, keep ? y[1] : 0.0);
+        sts_2(h + 2, keep ? y[2] : 0.0, keep ? y[3] : 0.0);
+        sts_2(h + 4, keep ? y[4] : 0.0, keep ? y[5] : 0.0);
+        sts_2(h + 6, keep ? y[6] : 0.0, 0.0);
+      }
     }
-    if (act7) kb[t * NJ + lane] = kv;
     __syncwarp();
-    F2 Hf;
-    Hf.k0 = HI[g * 8 + t4];
-    Hf.k1 = HI[g * 8 + 4 + t4];
-    // ---- K^T = Qxu Quu^-1, K -> HBM ----
-    F2 Qn[NBX], Kf[NBX];
+    F2 Lf, LTf;  // fragments of L^-1 and of its transpose
+    Lf.k0 = HI[t4 * 8 + g];
+    Lf.k1 = HI[(4 + t4) * 8 + g];
+    LTf.k0 = HI[g * 8 + t4];
+    LTf.k1 = HI[g * 8 + 4 + t4];
+    // ---- W = Qxu L^-T, K^T = W L^-1 -> HBM ----
+    F2 Wf[NBX], An[NBX];
+    double a7 = 0.0;
+    if (box) {
+      // row 7 of the A operand of tile row 0 := L^-1 (Quu k - 2 Qu), so that row 7 of the downdate is K^T (Quu k - 2 Qu)
+      double wvv[NJ];
+      gather7(wv, wvv);
+#pragma unroll
+      for (int c = 0; c < NJ; ++c) a7 += HI[c * 8 + r7] * wvv[c];
+      if (!act7) a7 = 0.0;
+    }
 #pragma unroll
     for (int a = 0; a < NBX; ++a) {
       const F2 Qf = frag_of(Qxu[a], lane);
+      T2 W = mkt(0.0, 0.0);
+      mma88(W, Qf, Lf);   // W[g][j] = sum_k Qxu[g][k] Linv[j][k]
+      Wf[a] = frag_of(W, lane);
       T2 KT = mkt(0.0, 0.0);
-      mma88(KT, Qf, Hf);  // KT[g][j] = K[j][7a + g]
+      mma88(KT, Wf[a], LTf);  // KT[g][j] = sum_k W[g][k] Linv[k][j] = K[j][7a + g]
       if (real_row) {
         double *Kt = Kb + (size_t)t * NJ * n + 7 * a + g;
         Kt[(2 * t4) * n] = KT.c0;
         if (t4 < 3) Kt[(2 * t4 + 1) * n] = KT.c1;
       }
-      Kf[a] = frag_of(KT, lane);
-      Qn[a].k0 = -Qf.k0;
-      Qn[a].k1 = -Qf.k1;
+      if (a == 0 && !box) {
+        // unconstrained step: row 7 of W is (L^-1 Qu)^T, of K^T it is k^T = (Quu^-1 Qu)^T;  Qu.k = k.Quu k = |L^-1 Qu|^2
+        if (row7) {
+          kb[t * NJ + 2 * t4] = KT.c0;
+          if (t4 < 3) kb[t * NJ + 2 * t4 + 1] = KT.c1;
+          const double s2 = W.c0 * W.c0 + W.c1 * W.c1;
+          dgp += s2;
+          dqp -= s2;
+        }
+      }
+      An[a].k0 = -Wf[a].k0;
+      An[a].k1 = -Wf[a].k1;
     }
-    // row 7 of the A operand of tile row 0 := +(Quu k - 2 Qu): row 7 of the update becomes Vx = Qx + K^T (Quu k - 2 Qu)
-    {
-      const double w0 = shfl_d(wv, t4), w1 = shfl_d(wv, 4 + t4);
+    if (box) {
+      const double w0 = shfl_d(a7, t4), w1 = shfl_d(a7, 4 + t4);
       if (row7) {
-        Qn[0].k0 = w0;
-        Qn[0].k1 = w1;
+        An[0].k0 = w0;
+        An[0].k1 = w1;
       }
     }
-    // ---- Vxx = Qxx - Qxu K (+ preg), upper tiles; padding cleaned; lower tiles by transposition ----
+    // ---- Vxx = Qxx - W W^T (+ preg), upper tiles (row 7 of tile row 0: Vx = Qx + K^T (Quu k - 2 Qu)); padding cleaned ----
     {
       const double p0 = dg0 ? preg : 0.0, p1 = dg1 ? preg : 0.0;
       const bool col7 = (t4 == 3);
@@ -600,7 +639,7 @@ FFMPC_DEV bool riccati_sweep(const Params &P, int b, double *sm, double preg, bo
         for (int bb = a; bb < NBX; ++bb) {
           const int id = (a == 0) ? bb : (a == 1 ? 2 + bb : 5);
           T2 v = Q[id];
-          mma88(v, Qn[a], Kf[bb]);
+          mma88(v, An[a], Wf[bb]);
           if (a == bb) { v.c0 += p0; v.c1 += p1; }
           if (col7) v.c1 = 0.0;                     // column 7: padding
           if (a > 0 && row7) v = mkt(0.0, 0.0);     // row 7 of the tile rows 1, 2: padding (tile row 0: Vx)

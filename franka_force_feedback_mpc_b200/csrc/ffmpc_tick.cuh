@@ -114,10 +114,12 @@ static __global__ void k_tick_policy(const __grid_constant__ Params P, TickArgs 
     raw[a] = tau[a];
     if (ff && pol.ff_inverse_actuation_model) raw[a] = (tau[a] - pol.ff_alpha_ctrl * xn[14 + a]) / fmax(1.0e-6, 1.0 - pol.ff_alpha_ctrl);
     raw_inf = fmax(raw_inf, fabs(raw[a]));
-    if (isnan(raw[a])) raw_inf = NAN;
+    if (isnan(raw[a])) raw_inf = NAN;  // np.max(np.abs(.)) propagates NaN
   }
   const double cost = ws.cost[b];
-  const bool unstable = !isfinite(cost) || cost > pol.max_solver_cost || !(raw_inf <= pol.max_tau_raw_inf);
+  // the reference's guard (crocoddyl_classical.py:393-403): `tau_raw_inf > max` is False for NaN -- a non-finite command
+  // does not trip the guard, `_safe_tau` below then holds the last command
+  const bool unstable = !isfinite(cost) || cost > pol.max_solver_cost || raw_inf > pol.max_tau_raw_inf;
   if (A.tau_raw) for (int a = 0; a < NJ; ++a) A.tau_raw[(size_t)b * NJ + a] = tau[a];
   if (unstable)
     for (int a = 0; a < NJ; ++a) raw[a] = bias[a] - pol.fallback_dq_damping * xn[NJ + a];

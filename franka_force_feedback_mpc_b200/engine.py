@@ -39,6 +39,7 @@ def _declare(lib):
     lib.ffmpc_tick_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.ffmpc_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.ffmpc_sync.argtypes = [C.c_void_p]
+    lib.ffmpc_get_info.argtypes = [C.c_void_p, C.c_void_p]
     lib.ffmpc_set_profiling.argtypes = [C.c_void_p, C.c_int]
     if hasattr(lib, "ffmpc_dfma_peak"):  # absent from the test-only host emulator build
         lib.ffmpc_dfma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -73,11 +74,12 @@ def dfma_peak_tflops(device: int = 0) -> float:
 
 
 class FFMPCEngine:
-    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec"; ``host_chunks``: how
-    ``solve_host`` pipelines result copies against compute (0 = auto).  Both only schedule work: results are bit-identical."""
+    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec"; ``sub_batches``: into how many
+    concurrently scheduled sub-batches (own workspace + stream) a batch is split (0 = auto).  Both only schedule work:
+    results are bit-identical."""
 
     def __init__(self, cfg: _abi.Config, model: _abi.Model, device: int = 0, max_batch: int = 1, _lib=None,
-                 line_search: str = "auto", host_chunks: int = 0):
+                 line_search: str = "auto", sub_batches: int = 0):
         self.lib = _lib if _lib is not None else load_library()
         self.cfg, self.model = cfg, model
         self.N = int(cfg.horizon)
@@ -88,7 +90,7 @@ class FFMPCEngine:
         opt = _abi.Options()
         self.lib.ffmpc_default_options(C.byref(opt))
         opt.line_search = _abi.LINE_SEARCH_MODES[line_search]
-        opt.host_chunks = int(host_chunks)
+        opt.sub_batches = int(sub_batches)
         rc = self.lib.ffmpc_create_ex(C.byref(cfg), C.byref(model), self.device, self.max_batch, C.byref(opt), C.byref(self._h))
         self._check(rc)
 
@@ -150,11 +152,13 @@ class FFMPCEngine:
 
     # ---- receding-horizon tick for the whole batch (ffmpc_tick_batch_host): shift, solve, policy, guard, filter ----
     def tick_host(self, mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias, policy: _abi.TickPolicy, max_iters: int,
-                  fixed_iters: bool = False, reset: bool = False, want_plan: bool = False) -> dict:
+                  fixed_iters: bool = False, reset: bool = False, want_plan: bool = False, tau_ref=None) -> dict:
         mode = np.ascontiguousarray(mode, dtype=np.int32).reshape(-1)
         B, N, nx = mode.size, self.N, self.nx
         arrs = dict(x_now=(B, nx), p_ref=(B, N + 1, 3), v_ref=(B, N + 1, 3), x_reg_ref=(B, 14), tau_bias=(B, 7))
         vals = dict(x_now=x_now, p_ref=p_ref, v_ref=v_ref, x_reg_ref=x_reg_ref, tau_bias=tau_bias)
+        if tau_ref is not None:
+            arrs["tau_ref"], vals["tau_ref"] = (B, 7), tau_ref
         s_in = _abi.TickIn()
         s_in.B, s_in.reset, s_in.mode = B, int(bool(reset)), ptr(mode)
         keep = [mode]
@@ -171,6 +175,12 @@ class FFMPCEngine:
             setattr(s_out, k, ptr(a))
         self._check(self.lib.ffmpc_tick_batch_host(self._h, C.byref(s_in), C.byref(policy), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
         return out
+
+    def info(self) -> dict:
+        i = _abi.Info()
+        self._check(self.lib.ffmpc_get_info(self._h, C.byref(i)))
+        return dict(sub_batches=i.sub_batches, sub_batch_capacity=i.sub_batch_capacity,
+                    line_search={v: k for k, v in _abi.LINE_SEARCH_MODES.items()}[i.line_search])
 
     def sync(self):
         self._check(self.lib.ffmpc_sync(self._h))

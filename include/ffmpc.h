@@ -183,13 +183,22 @@ void ffmpc_default_config(ffmpc_config *cfg, int variant);
 #define FFMPC_LS_QUEUE 1       /* one launch per step length over the compacted queue of instances that rejected the
                                   previous one (same trial sequence as the loop of SolverFDDP::solve)                  */
 #define FFMPC_LS_SPECULATIVE 2 /* every step length rolled out in one launch, decisions replayed in order (latency)   */
+#define FFMPC_MAX_SUB_BATCHES 16
 typedef struct ffmpc_options {
   int line_search; /* FFMPC_LS_*                                                                                     */
-  int host_chunks; /* ffmpc_solve_batch_host: 0 = auto, 1 = unsplit, k > 1 = k chunks whose device->host copies
-                      overlap the next chunk's solve                                                                 */
+  int sub_batches; /* A batch is solved as up to this many contiguous sub-batches, each with its own workspace and
+                      CUDA stream, stream priority falling with the index: later sub-batches fill what the earlier
+                      ones leave idle (kernel tails, the late line-search passes), and in the host API a finished
+                      sub-batch's results cross PCIe while the others are still solved.  0 = auto (1 below 4096
+                      instances of capacity, 2 below 16384, else 4), 1 = none, up to FFMPC_MAX_SUB_BATCHES.         */
   int reserved[6];
 } ffmpc_options;
 void ffmpc_default_options(ffmpc_options *opt);
+
+typedef struct ffmpc_info {  /* what a handle resolved its options to */
+  int sub_batches, sub_batch_capacity, line_search;
+  int reserved[5];
+} ffmpc_info;
 
 /* One handle per GPU; owns workspace for up to max_batch instances; not thread-safe. */
 int ffmpc_create(const ffmpc_config *cfg, const ffmpc_model *model, int device, int max_batch,
@@ -199,9 +208,11 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
                     const ffmpc_options *opt, ffmpc_handle **out);
 void ffmpc_destroy(ffmpc_handle *h);
 
-/* Batched solve, DEVICE pointers, stream-ordered (returns after enqueueing; `stream` is a
- * cudaStream_t, NULL = default stream).  fixed_iters != 0 disables the converged early exit
- * (`was_feasible && stop < th_stop`), as the throughput benchmark requires. */
+/* Batched solve, DEVICE pointers, stream-ordered: the work is enqueued behind everything already on `stream`
+ * (a cudaStream_t; NULL = the handle's OWN stream, not the legacy default stream: order it against other work with
+ * ffmpc_sync), and `stream` continues only after the whole batch is done, as after a single kernel launch (internally
+ * the sub-batches fan out to the handle's streams and join back).  Returns after enqueueing.  fixed_iters != 0 disables
+ * the converged early exit (`was_feasible && stop < th_stop`), as the throughput benchmark requires. */
 int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
                       const ffmpc_batch_out *out, void *stream);
 
@@ -225,8 +236,11 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
  *   command filter (`_safe_tau`)                      crocoddyl_classical.py:260-284
  * The previous plan (xs, us, K of the last solve), the last command and the last mode stay in the handle between
  * ticks, so a closed-loop sweep needs no host round trip besides x_now in / tau_cmd out.  Solves on every tick
- * (`mpc_update_steps = 1`, the value of every preset).  Do not interleave ffmpc_solve_batch calls on the same
- * handle between ticks: they overwrite the stored plan. */
+ * (`mpc_update_steps = 1`, the value of every preset).  The stored plans live in the solver workspace: a tick with
+ * another batch size than the previous one, or after any ffmpc_solve_batch[_host] call on the handle, starts from
+ * scratch as if `reset` were set.
+ * Deviation from the reference, non-finite corner only: when the new plan's first control is not finite the reference
+ * keeps running the policy on the PREVIOUS plan; here the plan is dropped and the last command (FF: tau_hat) is held. */
 typedef struct ffmpc_tick_policy {
   int use_feedback_policy;       /* cfg.use_feedback_policy                                       */
   int ff_use_tau_interpolation;  /* FF: Eq. 14 interpolation on / off                             */
@@ -249,6 +263,7 @@ typedef struct ffmpc_tick_in {
   const double *v_ref;     /* [B, N+1, 3]                                                      */
   const double *x_reg_ref; /* [B, 14]                                                          */
   const double *tau_bias;  /* [B, 7] obs.tau_bias: fallback torque of the unstable guard       */
+  const double *tau_ref;   /* [B, 7] or NULL: tau_reg reference; NULL -> g(q_now) (torque_ref_mode "gravity_x0") */
 } ffmpc_tick_in;
 
 typedef struct ffmpc_tick_out {  /* every pointer may be NULL */
@@ -287,7 +302,8 @@ int ffmpc_get_profile(ffmpc_handle *h, double *ms /*[FFMPC_NFAM]*/, int *launche
  * the measured roofline denominator of this compute-bound path (bench.py).  Best of 5 timed runs. */
 int ffmpc_dfma_peak(int device, double *tflops, double *ms /* nullable */);
 
-int ffmpc_sync(ffmpc_handle *h);
+int ffmpc_sync(ffmpc_handle *h);  /* waits for everything enqueued on the handle's streams */
+int ffmpc_get_info(ffmpc_handle *h, ffmpc_info *info);
 const char *ffmpc_last_error(void);
 const char *ffmpc_version(void);
 

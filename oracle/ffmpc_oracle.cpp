@@ -52,29 +52,60 @@ constexpr int NZ = 21;  // (q, v, u) stacking of the inner DAM
 std::atomic<long long> g_rollouts{0}, g_iterations{0};
 std::atomic<long long> g_trial_hist[32];
 
+// The scalar of every computation below.  double: the oracle proper (bit-for-bit the round-1 oracle).  __float128
+// (-DFFMPC_ORACLE_QUAD, libffmpc_oracle_quad.so): the same source as a higher-precision ARBITER -- when the fp64 GPU
+// result and the fp64 oracle disagree at the 1e-8 level after ten nonlinear iterations, the quad build says which of
+// the two moved (tests/test_gpu_parity.py).  Inputs, outputs, model and config stay fp64 at the C boundary.
+#ifdef FFMPC_ORACLE_QUAD
+#include <quadmath.h>
+typedef __float128 real;
+#define RPI (4 * atanq(1))
+inline real rsqrt_(real x) { return sqrtq(x); }
+inline real rsin(real x) { return sinq(x); }
+inline real rcos(real x) { return cosq(x); }
+inline real racos(real x) { return acosq(x); }
+inline real rabs(real x) { return fabsq(x); }
+inline bool rfinite(real x) { return finiteq(x) != 0; }
+inline real rldexp(real x, int e) { return ldexpq(x, e); }
+#else
+typedef double real;
+#define RPI 3.14159265358979323846
+inline real rsqrt_(real x) { return std::sqrt(x); }
+inline real rsin(real x) { return std::sin(x); }
+inline real rcos(real x) { return std::cos(x); }
+inline real racos(real x) { return std::acos(x); }
+inline real rabs(real x) { return std::fabs(x); }
+inline bool rfinite(real x) { return std::isfinite(x); }
+inline real rldexp(real x, int e) { return std::ldexp(x, e); }
+#endif
+inline real rmin(real a, real b) { return (b < a) ? b : a; }  // std::min / std::max semantics
+inline real rmax(real a, real b) { return (a < b) ? b : a; }
+inline real rinf() { return std::numeric_limits<double>::infinity(); }
+inline real rnan() { return std::numeric_limits<double>::quiet_NaN(); }
+
 struct Dual {
-  double v;
-  double d[NZ];
+  real v;
+  real d[NZ];
   Dual() : v(0.0) { std::memset(d, 0, sizeof(d)); }
-  Dual(double x) : v(x) { std::memset(d, 0, sizeof(d)); }  // NOLINT implicit on purpose
+  Dual(real x) : v(x) { std::memset(d, 0, sizeof(d)); }  // NOLINT implicit on purpose
 };
 inline Dual operator+(const Dual &a, const Dual &b) { Dual r; r.v = a.v + b.v; for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] + b.d[i]; return r; }
 inline Dual operator-(const Dual &a, const Dual &b) { Dual r; r.v = a.v - b.v; for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] - b.d[i]; return r; }
 inline Dual operator-(const Dual &a) { Dual r; r.v = -a.v; for (int i = 0; i < NZ; ++i) r.d[i] = -a.d[i]; return r; }
 inline Dual operator*(const Dual &a, const Dual &b) { Dual r; r.v = a.v * b.v; for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * b.v + a.v * b.d[i]; return r; }
-inline Dual operator/(const Dual &a, const Dual &b) { Dual r; const double ib = 1.0 / b.v; r.v = a.v * ib; for (int i = 0; i < NZ; ++i) r.d[i] = (a.d[i] - r.v * b.d[i]) * ib; return r; }
+inline Dual operator/(const Dual &a, const Dual &b) { Dual r; const real ib = 1.0 / b.v; r.v = a.v * ib; for (int i = 0; i < NZ; ++i) r.d[i] = (a.d[i] - r.v * b.d[i]) * ib; return r; }
 inline Dual &operator+=(Dual &a, const Dual &b) { a = a + b; return a; }
 inline Dual &operator-=(Dual &a, const Dual &b) { a = a - b; return a; }
-inline Dual sqrt(const Dual &a) { Dual r; r.v = std::sqrt(a.v); const double s = 0.5 / r.v; for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
-inline Dual sin(const Dual &a) { Dual r; r.v = std::sin(a.v); const double c = std::cos(a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * c; return r; }
-inline Dual cos(const Dual &a) { Dual r; r.v = std::cos(a.v); const double s = -std::sin(a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
-inline Dual acos(const Dual &a) { Dual r; r.v = std::acos(a.v); const double s = -1.0 / std::sqrt(1.0 - a.v * a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
-inline double val(double x) { return x; }
-inline double val(const Dual &x) { return x.v; }
-using std::acos;
-using std::cos;
-using std::sin;
-using std::sqrt;
+inline Dual sqrt(const Dual &a) { Dual r; r.v = rsqrt_(a.v); const real s = 0.5 / r.v; for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
+inline Dual sin(const Dual &a) { Dual r; r.v = rsin(a.v); const real c = rcos(a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * c; return r; }
+inline Dual cos(const Dual &a) { Dual r; r.v = rcos(a.v); const real s = -rsin(a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
+inline Dual acos(const Dual &a) { Dual r; r.v = racos(a.v); const real s = -1.0 / rsqrt_(1.0 - a.v * a.v); for (int i = 0; i < NZ; ++i) r.d[i] = a.d[i] * s; return r; }
+inline real val(real x) { return x; }
+inline real val(const Dual &x) { return x.v; }
+inline real sqrt(real x) { return rsqrt_(x); }
+inline real sin(real x) { return rsin(x); }
+inline real cos(real x) { return rcos(x); }
+inline real acos(real x) { return racos(x); }
 
 // ----------------------------------------------------------------------------------------------
 // tiny 3-vector / 3x3 algebra, generic in the scalar
@@ -106,13 +137,13 @@ template <class T> M3<T> transpose(const M3<T> &A) {
   return C;
 }
 template <class T> V3<T> col(const M3<T> &A, int j) { return {A.m[0][j], A.m[1][j], A.m[2][j]}; }
-template <class T> M3<T> m3_from(const double *r) {
+template <class T, class S> M3<T> m3_from(const S *r) {
   M3<T> C;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) C.m[i][j] = T(r[3 * i + j]);
   return C;
 }
-template <class T> V3<T> v3_from(const double *r) { return {T(r[0]), T(r[1]), T(r[2])}; }
+template <class T, class S> V3<T> v3_from(const S *r) { return {T(r[0]), T(r[1]), T(r[2])}; }
 template <class T> S6<T> operator+(const S6<T> &a, const S6<T> &b) { return {a.l + b.l, a.a + b.a}; }
 template <class T> S6<T> operator*(const S6<T> &a, const T &s) { return {a.l * s, a.a * s}; }
 // motion x motion
@@ -266,7 +297,7 @@ template <class T, int N> void chol_solve(const T L[N][N], int n, T *b) {
 template <class T> V3<T> log3(const M3<T> &R) {
   const T tr = R.m[0][0] + R.m[1][1] + R.m[2][2];
   T t;
-  const double trv = val(tr);
+  const real trv = val(tr);
   if (trv >= 3.0 - 1e-14) {
     t = T(0.5);
   } else {
@@ -282,55 +313,55 @@ template <class T> V3<T> log3(const M3<T> &R) {
 // cost accumulation: CostModelSum of CostModelResidual terms
 // ----------------------------------------------------------------------------------------------
 struct CostAcc {
-  double cost = 0.0;
-  double Lz[NZ];
-  double Lzz[NZ][NZ];
+  real cost = 0.0;
+  real Lz[NZ];
+  real Lzz[NZ][NZ];
   CostAcc() {
     std::memset(Lz, 0, sizeof(Lz));
     std::memset(Lzz, 0, sizeof(Lzz));
   }
 };
-inline void acc_jac(CostAcc &, double, const double &, double, double) {}
-inline void acc_jac(CostAcc &c, double w, const Dual &r, double Ar, double Arr) {
+inline void acc_jac(CostAcc &, real, const real &, real, real) {}
+inline void acc_jac(CostAcc &c, real w, const Dual &r, real Ar, real Arr) {
   if (Ar != 0.0)
     for (int a = 0; a < NZ; ++a) c.Lz[a] += w * Ar * r.d[a];
   if (Arr != 0.0)
     for (int a = 0; a < NZ; ++a) {
-      const double wa = w * Arr * r.d[a];
+      const real wa = w * Arr * r.d[a];
       if (wa != 0.0)
         for (int b = 0; b < NZ; ++b) c.Lzz[a][b] += wa * r.d[b];
     }
 }
 // ActivationModelWeightedQuad (w == nullptr -> plain quad)
-template <class T> void add_quad(CostAcc &c, double weight, int nr, const T *r, const double *aw) {
-  double a = 0.0;
+template <class T, class W> void add_quad(CostAcc &c, real weight, int nr, const T *r, const W *aw) {
+  real a = 0.0;
   for (int i = 0; i < nr; ++i) {
-    const double wi = aw ? aw[i] : 1.0;
-    const double ri = val(r[i]);
+    const real wi = aw ? aw[i] : 1.0;
+    const real ri = val(r[i]);
     a += wi * ri * ri;
     acc_jac(c, weight, r[i], wi * ri, wi);
   }
   c.cost += weight * 0.5 * a;
 }
 // ActivationModelQuadraticBarrier(ActivationBounds(lb, ub, 1.0))
-template <class T> void add_barrier(CostAcc &c, double weight, int nr, const T *r, const double *lb, const double *ub) {
-  double a = 0.0;
+template <class T> void add_barrier(CostAcc &c, real weight, int nr, const T *r, const real *lb, const real *ub) {
+  real a = 0.0;
   for (int i = 0; i < nr; ++i) {
-    const double ri = val(r[i]);
-    const double lo = std::min(ri - lb[i], 0.0);
-    const double hi = std::max(ri - ub[i], 0.0);
+    const real ri = val(r[i]);
+    const real lo = rmin(ri - lb[i], 0.0);
+    const real hi = rmax(ri - ub[i], 0.0);
     a += lo * lo + hi * hi;
-    const double Arr = ((ri - lb[i]) <= 0.0 ? 1.0 : 0.0) + ((ri - ub[i]) >= 0.0 ? 1.0 : 0.0);
+    const real Arr = ((ri - lb[i]) <= 0.0 ? 1.0 : 0.0) + ((ri - ub[i]) >= 0.0 ? 1.0 : 0.0);
     acc_jac(c, weight, r[i], lo + hi, Arr);
   }
   c.cost += weight * 0.5 * a;
 }
 
 struct NodeRefs {
-  const double *p_ref;      // [3]
-  const double *v_ref;      // [3]
-  const double *x_reg_ref;  // [14]
-  const double *tau_ref;    // [7]
+  const real *p_ref;      // [3]
+  const real *v_ref;      // [3]
+  const real *x_reg_ref;  // [14]
+  const real *tau_ref;    // [7]
 };
 
 template <class T> struct DamOut {
@@ -356,7 +387,7 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
   const S6<T> &v7 = k.v[NJ - 1];
   const V3<T> vf = v7.l + cross(v7.a, k.pf);  // velocity of the frame origin
   const V3<T> wf = v7.a;
-  const double z_target = ref.p_ref[2] - cfg.z_press;
+  const real z_target = ref.p_ref[2] - cfg.z_press;
   const V3<T> p_contact = mk(T(ref.p_ref[0]), T(ref.p_ref[1]), T(z_target));
 
   for (int i = 0; i < 3; ++i) out.lam[i] = T(0.0);
@@ -439,42 +470,42 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
   const V3<T> dp_ref = k.pf - v3_from<T>(ref.p_ref);
   if (!contact) {  // "ee_pos"
     const T r[3] = {dp_ref.x, dp_ref.y, dp_ref.z};
-    const double aw[3] = {1.0, 1.0, 2.5};
+    const real aw[3] = {1.0, 1.0, 2.5};
     add_quad<T>(c, cfg.w_ee_pos, 3, r, aw);
   } else {
     {  // "ee_vxy"
       const T r[6] = {vf.x - T(ref.v_ref[0]), vf.y - T(ref.v_ref[1]), vf.z, wf.x, wf.y, wf.z};
-      const double aw[6] = {1.0, 1.0, 0.0, 0.0, 0.0, 0.0};
+      const real aw[6] = {1.0, 1.0, 0.0, 0.0, 0.0, 0.0};
       add_quad<T>(c, cfg.w_tangent_vel, 6, r, aw);
     }
     {  // "ee_xy"
       const T r[3] = {dp_ref.x, dp_ref.y, dp_ref.z};
-      const double aw[3] = {1.0, 1.0, 0.0};
+      const real aw[3] = {1.0, 1.0, 0.0};
       add_quad<T>(c, cfg.w_tangent_pos, 3, r, aw);
     }
     if (cfg.w_fn > 0.0) {  // "fn_track"
       if (nc == 1) {
         const T r[1] = {with_control ? out.lam[2] - T(cfg.fn_des) : T(0.0)};
-        const double aw[1] = {1.0};
+        const real aw[1] = {1.0};
         add_quad<T>(c, cfg.w_fn, 1, r, aw);
       } else {
         T r[3] = {out.lam[0], out.lam[1], out.lam[2] - T(cfg.fn_des)};
         if (!with_control) r[0] = r[1] = r[2] = T(0.0);
-        const double aw[3] = {0.0, 0.0, 1.0};
+        const real aw[3] = {0.0, 0.0, 1.0};
         add_quad<T>(c, cfg.w_fn, 3, r, aw);
       }
     }
     if (nc == 3 && cfg.w_friction_cone > 0.0) {  // "friction_cone" (crocoddyl_classical.py:678-686)
       // FrictionCone(R = I, mu, nf = 4, inner_appr = false) [upstream]: facet rows (-mu n + t_i)^T, t_i = (cos, sin, 0) at
       // i 2pi/nf, bounds (-inf, 0]; last row n^T, bounds [min_nforce = 0, inf).  Margin: :891-904.
-      const double inf = std::numeric_limits<double>::infinity();
-      const double eps = std::max(cfg.friction_margin, 0.0);
-      const double pi = 3.14159265358979323846;
+      const real inf = rinf();
+      const real eps = rmax(cfg.friction_margin, 0.0);
+      const real pi = RPI;
       T r[5];
-      double lb[5], ub[5];
+      real lb[5], ub[5];
       for (int i = 0; i < 4; ++i) {
-        const double th = 2.0 * pi / 4.0 * i;
-        r[i] = with_control ? T(std::cos(th)) * out.lam[0] + T(std::sin(th)) * out.lam[1] - T(cfg.mu) * out.lam[2] : T(0.0);
+        const real th = 2.0 * pi / 4.0 * i;
+        r[i] = with_control ? T(rcos(th)) * out.lam[0] + T(rsin(th)) * out.lam[1] - T(cfg.mu) * out.lam[2] : T(0.0);
         lb[i] = -inf;
         ub[i] = 0.0 - eps;
       }
@@ -486,7 +517,7 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
     if (cfg.w_plane_z > 0.0) {  // "plane_z"
       const V3<T> d = k.pf - p_contact;
       const T r[3] = {d.x, d.y, d.z};
-      const double aw[3] = {0.0, 0.0, 1.0};
+      const real aw[3] = {0.0, 0.0, 1.0};
       add_quad<T>(c, cfg.w_plane_z, 3, r, aw);
     }
   }
@@ -496,18 +527,18 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
       r[i] = q[i] - T(ref.x_reg_ref[i]);
       r[NJ + i] = qd[i] - T(ref.x_reg_ref[NJ + i]);
     }
-    add_quad<T>(c, cfg.w_posture, 14, r, nullptr);
+    add_quad<T>(c, cfg.w_posture, 14, r, (const real *)nullptr);
   }
   if (cfg.w_q_soft_limits > 0.0) {  // "q_soft_limits"
     T r[14];
-    double lb[14], ub[14];
+    real lb[14], ub[14];
     for (int i = 0; i < NJ; ++i) {
       r[i] = q[i] - T(cfg.q_soft_ref[i]);
       r[NJ + i] = qd[i];
       lb[i] = cfg.q_soft_lb[i];
       ub[i] = cfg.q_soft_ub[i];
-      lb[NJ + i] = -std::numeric_limits<double>::infinity();
-      ub[NJ + i] = std::numeric_limits<double>::infinity();
+      lb[NJ + i] = -rinf();
+      ub[NJ + i] = rinf();
     }
     add_barrier<T>(c, cfg.w_q_soft_limits, 14, r, lb, ub);
   }
@@ -515,15 +546,15 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
     {  // "tau_reg"
       T r[NJ];
       for (int i = 0; i < NJ; ++i) r[i] = with_control ? u[i] - T(ref.tau_ref[i]) : T(0.0);
-      add_quad<T>(c, cfg.w_tau, NJ, r, nullptr);
+      add_quad<T>(c, cfg.w_tau, NJ, r, (const real *)nullptr);
     }
     if (cfg.w_tau_soft_limits > 0.0) {  // "tau_soft_limits"
-      double mn = cfg.tau_limits[0];
-      for (int i = 1; i < NJ; ++i) mn = std::min(mn, cfg.tau_limits[i]);
-      double margin = std::max(cfg.tau_soft_limit_margin, 0.0);
-      margin = std::min(margin, mn - 1.0e-6);
+      real mn = cfg.tau_limits[0];
+      for (int i = 1; i < NJ; ++i) mn = rmin(mn, cfg.tau_limits[i]);
+      real margin = rmax(cfg.tau_soft_limit_margin, 0.0);
+      margin = rmin(margin, mn - 1.0e-6);
       T r[NJ];
-      double lb[NJ], ub[NJ];
+      real lb[NJ], ub[NJ];
       for (int i = 0; i < NJ; ++i) {
         r[i] = with_control ? u[i] : T(0.0);
         lb[i] = -cfg.tau_limits[i] + margin;
@@ -533,21 +564,21 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
     }
   }
   if (contact && cfg.w_unilateral > 0.0) {  // "unilateral"
-    const double inf = std::numeric_limits<double>::infinity();
+    const real inf = rinf();
     if (nc == 1) {
       const T r[1] = {with_control ? out.lam[2] : T(0.0)};
-      const double lb[1] = {cfg.friction_margin}, ub[1] = {inf};
+      const real lb[1] = {cfg.friction_margin}, ub[1] = {inf};
       add_barrier<T>(c, cfg.w_unilateral, 1, r, lb, ub);
     } else {
       T r[3] = {out.lam[0], out.lam[1], out.lam[2]};
       if (!with_control) r[0] = r[1] = r[2] = T(0.0);
-      const double lb[3] = {-inf, -inf, cfg.friction_margin}, ub[3] = {inf, inf, inf};
+      const real lb[3] = {-inf, -inf, cfg.friction_margin}, ub[3] = {inf, inf, inf};
       add_barrier<T>(c, cfg.w_unilateral, 3, r, lb, ub);
     }
   }
   if (state_reg) {  // "v_damp"
     T r[14];
-    double aw[14];
+    real aw[14];
     for (int i = 0; i < NJ; ++i) {
       r[i] = q[i];
       r[NJ + i] = qd[i];
@@ -558,12 +589,12 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
   }
   if (contact && cfg.w_vz > 0.0) {  // "vz_damp"
     const T r[6] = {vf.x, vf.y, vf.z, wf.x, wf.y, wf.z};
-    const double aw[6] = {0.0, 0.0, 1.0, 0.0, 0.0, 0.0};
+    const real aw[6] = {0.0, 0.0, 1.0, 0.0, 0.0, 0.0};
     add_quad<T>(c, cfg.w_vz, 6, r, aw);
   }
   {  // "w_damp"
     const T r[6] = {vf.x, vf.y, vf.z, wf.x, wf.y, wf.z};
-    const double aw[6] = {0.0, 0.0, 0.0, cfg.w_wdamp_weights[0], cfg.w_wdamp_weights[1], cfg.w_wdamp_weights[2]};
+    const real aw[6] = {0.0, 0.0, 0.0, cfg.w_wdamp_weights[0], cfg.w_wdamp_weights[1], cfg.w_wdamp_weights[2]};
     add_quad<T>(c, cfg.w_wdamp, 6, r, aw);
   }
 }
@@ -573,12 +604,12 @@ void dam_eval(const ffmpc_model &mdl, const ffmpc_config &cfg, int mode, bool te
 // ----------------------------------------------------------------------------------------------
 struct NodeData {
   int nx = 0;
-  double xnext[21];
-  double cost = 0.0;
-  double lam[3] = {0, 0, 0};
+  real xnext[21];
+  real cost = 0.0;
+  real lam[3] = {0, 0, 0};
   bool ok = true;
   // derivatives (only after calcDiff)
-  double Fx[21][21], Fu[21][7], Lx[21], Lu[7], Lxx[21][21], Lxu[21][7], Luu[7][7];
+  real Fx[21][21], Fu[21][7], Lx[21], Lu[7], Lxx[21][21], Lxu[21][7], Luu[7][7];
 };
 
 struct Problem {
@@ -587,20 +618,20 @@ struct Problem {
   int mode;
   int N;
   int nx;
-  std::vector<double> p_ref, v_ref;  // [(N+1)*3]
-  double x_reg_ref[14];
-  double tau_ref[7];
-  double y_ref[21];
-  double x0[21];
+  std::vector<real> p_ref, v_ref;  // [(N+1)*3]
+  real x_reg_ref[14];
+  real tau_ref[7];
+  real y_ref[21];
+  real x0[21];
 };
 
-void lpf_soft(const ffmpc_config &cfg, const double *w, double &cost, double *grad, double *hess) {
+void lpf_soft(const ffmpc_config &cfg, const real *w, real &cost, real *grad, real *hess) {
   // _AugmentedLPFActionModel._soft_limit_terms (crocoddyl_force_feedback.py:195-209)
   cost = 0.0;
-  const double margin = std::max(cfg.tau_soft_limit_margin, 0.0);
+  const real margin = rmax(cfg.tau_soft_limit_margin, 0.0);
   for (int i = 0; i < NJ; ++i) {
-    const double lim = std::max(cfg.tau_limits[i] - margin, 1.0e-9);
-    const double over = std::max(std::fabs(w[i]) - lim, 0.0);
+    const real lim = rmax(cfg.tau_limits[i] - margin, 1.0e-9);
+    const real over = rmax(rabs(w[i]) - lim, 0.0);
     const bool active = over > 0.0;
     cost += over * over;
     grad[i] = active ? over * (w[i] > 0.0 ? 1.0 : (w[i] < 0.0 ? -1.0 : 0.0)) : 0.0;
@@ -610,24 +641,24 @@ void lpf_soft(const ffmpc_config &cfg, const double *w, double &cost, double *gr
 }
 
 // evaluates knot t at (x, u); diff = false -> calc only.  t == N is the terminal model.
-void node_eval(const Problem &P, int t, const double *x, const double *u_in, bool diff, NodeData &nd) {
+void node_eval(const Problem &P, int t, const real *x, const real *u_in, bool diff, NodeData &nd) {
   const ffmpc_config &cfg = P.cfg;
   const bool ff = cfg.variant == FFMPC_VARIANT_FF;
   const bool terminal = (t == P.N);
-  const double dt = cfg.dt_ocp;
+  const real dt = cfg.dt_ocp;
   const int nx = P.nx;
   nd.nx = nx;
   NodeRefs ref{&P.p_ref[3 * t], &P.v_ref[3 * t], P.x_reg_ref, P.tau_ref};
-  double zero7[NJ] = {0, 0, 0, 0, 0, 0, 0};
+  real zero7[NJ] = {0, 0, 0, 0, 0, 0, 0};
   // FF: the inner control is the torque *state*; the wrapper always calls inner.calc(x_mb, tau),
   // so the FF terminal node uses the RUNNING form of the inner Euler model (quirk a16).
-  const double *u_inner = ff ? (x + 14) : (terminal ? zero7 : u_in);
-  const double *w = ff ? (terminal ? zero7 : u_in) : nullptr;
+  const real *u_inner = ff ? (x + 14) : (terminal ? zero7 : u_in);
+  const real *w = ff ? (terminal ? zero7 : u_in) : nullptr;
   const bool with_control = ff ? true : !terminal;
   const bool running_form = ff ? true : !terminal;
 
-  double a[NJ];
-  double da[NJ][NZ];
+  real a[NJ];
+  real da[NJ][NZ];
   CostAcc c;
   if (diff) {
     Dual q[NJ], qd[NJ], uu[NJ];
@@ -646,8 +677,8 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
     c = o.c;
     nd.ok = o.ok;
   } else {
-    DamOut<double> o;
-    dam_eval<double>(P.mdl, cfg, P.mode, terminal, with_control, ref, x, x + NJ, u_inner, o);
+    DamOut<real> o;
+    dam_eval<real>(P.mdl, cfg, P.mode, terminal, with_control, ref, x, x + NJ, u_inner, o);
     for (int i = 0; i < NJ; ++i) a[i] = o.a[i];
     for (int i = 0; i < 3; ++i) nd.lam[i] = o.lam[i];
     c = o.c;
@@ -655,7 +686,7 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
   }
 
   // ---- IntegratedActionModelEuler ----
-  double xn[14], cost;
+  real xn[14], cost;
   if (running_form) {
     for (int i = 0; i < NJ; ++i) {
       xn[i] = x[i] + (dt * x[NJ + i] + dt * dt * a[i]);
@@ -666,9 +697,9 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
     for (int i = 0; i < 14; ++i) xn[i] = x[i];
     cost = c.cost;
   }
-  const double sc = running_form ? dt : 1.0;
+  const real sc = running_form ? dt : 1.0;
   // inner derivatives over z = (x_mb, u_inner)
-  double Fz[14][NZ];
+  real Fz[14][NZ];
   if (diff) {
     for (int i = 0; i < 14; ++i)
       for (int j = 0; j < NZ; ++j) Fz[i][j] = 0.0;
@@ -703,25 +734,25 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
   }
 
   // ---- _AugmentedLPFActionModel (crocoddyl_force_feedback.py:211-290) ----
-  const double alpha = std::min(std::max(cfg.ff_alpha, 0.0), 0.999999);
-  const double beta = 1.0 - alpha;
+  const real alpha = rmin(rmax(cfg.ff_alpha, 0.0), 0.999999);
+  const real beta = 1.0 - alpha;
   for (int i = 0; i < 14; ++i) nd.xnext[i] = xn[i];
   for (int i = 0; i < NJ; ++i) nd.xnext[14 + i] = alpha * x[14 + i] + beta * w[i];
-  const double w_y = std::max(cfg.w_y, 0.0), w_w = std::max(cfg.w_w, 0.0), w_soft = std::max(cfg.w_w_soft_limits, 0.0);
+  const real w_y = rmax(cfg.w_y, 0.0), w_w = rmax(cfg.w_w, 0.0), w_soft = rmax(cfg.w_w_soft_limits, 0.0);
   if (w_y > 0.0) {
-    double s = 0.0;
+    real s = 0.0;
     for (int i = 0; i < 21; ++i) {
-      const double dy = x[i] - P.y_ref[i];
+      const real dy = x[i] - P.y_ref[i];
       s += cfg.y_reg_weights[i] * cfg.y_reg_weights[i] * dy * dy;
     }
     cost += 0.5 * w_y * s;
   }
   if (w_w > 0.0) {
-    double s = 0.0;
+    real s = 0.0;
     for (int i = 0; i < NJ; ++i) s += w[i] * w[i];
     cost += 0.5 * w_w * s;
   }
-  double csoft = 0.0, gsoft[NJ], hsoft[NJ];
+  real csoft = 0.0, gsoft[NJ], hsoft[NJ];
   if (w_soft > 0.0) {
     lpf_soft(cfg, w, csoft, gsoft, hsoft);
     cost += w_soft * csoft;
@@ -749,7 +780,7 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
   }
   if (w_y > 0.0)
     for (int i = 0; i < 21; ++i) {
-      const double wy2 = cfg.y_reg_weights[i] * cfg.y_reg_weights[i];
+      const real wy2 = cfg.y_reg_weights[i] * cfg.y_reg_weights[i];
       nd.Lx[i] += w_y * wy2 * (x[i] - P.y_ref[i]);
       nd.Lxx[i][i] += w_y * wy2;
     }
@@ -769,43 +800,43 @@ void node_eval(const Problem &P, int t, const double *x, const double *u_in, boo
 // BoxQP (Tassa 2014 projected Newton; crocoddyl::BoxQP) -- SURVEY App. A.8
 // ----------------------------------------------------------------------------------------------
 struct BoxQPSol {
-  double x[NJ];
+  real x[NJ];
   int free_idx[NJ], clamped_idx[NJ];
   int nf = 0, ncl = 0;
-  double Hff_inv[NJ][NJ];
+  real Hff_inv[NJ][NJ];
   bool ok = true;
 };
 
-bool boxqp_free_inverse(const double H[NJ][NJ], double reg, BoxQPSol &s, double Lff[NJ][NJ]) {
+bool boxqp_free_inverse(const real H[NJ][NJ], real reg, BoxQPSol &s, real Lff[NJ][NJ]) {
   for (int i = 0; i < s.nf; ++i)
     for (int j = 0; j < s.nf; ++j) Lff[i][j] = H[s.free_idx[i]][s.free_idx[j]] + ((i == j) ? reg : 0.0);
-  if (!chol<double, NJ>(Lff, s.nf)) return false;
+  if (!chol<real, NJ>(Lff, s.nf)) return false;
   for (int j = 0; j < s.nf; ++j) {
-    double e[NJ];
+    real e[NJ];
     for (int i = 0; i < s.nf; ++i) e[i] = (i == j) ? 1.0 : 0.0;
-    chol_solve<double, NJ>(Lff, s.nf, e);
+    chol_solve<real, NJ>(Lff, s.nf, e);
     for (int i = 0; i < s.nf; ++i) s.Hff_inv[i][j] = e[i];
   }
   return true;
 }
 
-void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *q, const double *lb, const double *ub,
-                 const double *xinit, BoxQPSol &s) {
+void boxqp_solve(const ffmpc_config &cfg, const real H[NJ][NJ], const real *q, const real *lb, const real *ub,
+                 const real *xinit, BoxQPSol &s) {
   const int n = NJ;
-  double x[NJ], g[NJ], dx[NJ], xnew[NJ], Lff[NJ][NJ];
-  for (int i = 0; i < n; ++i) x[i] = std::max(std::min(xinit[i], ub[i]), lb[i]);
+  real x[NJ], g[NJ], dx[NJ], xnew[NJ], Lff[NJ][NJ];
+  for (int i = 0; i < n; ++i) x[i] = rmax(rmin(xinit[i], ub[i]), lb[i]);
   s.ok = true;
   unsigned inv_mask = 0xffffffffu;
   for (int k = 0; k < cfg.boxqp_maxiter; ++k) {
     s.nf = s.ncl = 0;
     for (int i = 0; i < n; ++i) {
-      double gi = q[i];
+      real gi = q[i];
       for (int j = 0; j < n; ++j) gi += H[i][j] * x[j];
       g[i] = gi;
     }
-    double gnorm = 0.0;
+    real gnorm = 0.0;
     for (int j = 0; j < n; ++j) {
-      gnorm = std::max(gnorm, std::fabs(g[j]));
+      gnorm = rmax(gnorm, rabs(g[j]));
       if ((x[j] == lb[j] && g[j] > 0.0) || (x[j] == ub[j] && g[j] < 0.0)) s.clamped_idx[s.ncl++] = j;
       else s.free_idx[s.nf++] = j;
     }
@@ -829,33 +860,33 @@ void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *
       break;
     }
     inv_mask = mask;
-    double dxf[NJ];
+    real dxf[NJ];
     for (int i = 0; i < s.nf; ++i) {
       const int fi = s.free_idx[i];
-      double r = -q[fi];
+      real r = -q[fi];
       for (int j = 0; j < s.ncl; ++j) r -= H[fi][s.clamped_idx[j]] * x[s.clamped_idx[j]];
       dxf[i] = r;
     }
-    chol_solve<double, NJ>(Lff, s.nf, dxf);
+    chol_solve<real, NJ>(Lff, s.nf, dxf);
     for (int i = 0; i < n; ++i) dx[i] = 0.0;
     for (int i = 0; i < s.nf; ++i) dx[s.free_idx[i]] = dxf[i] - x[s.free_idx[i]];
     // line search
-    auto fval = [&](const double *y) {
-      double f = 0.0;
+    auto fval = [&](const real *y) {
+      real f = 0.0;
       for (int i = 0; i < n; ++i) {
-        double hy = 0.0;
+        real hy = 0.0;
         for (int j = 0; j < n; ++j) hy += H[i][j] * y[j];
         f += 0.5 * y[i] * hy + q[i] * y[i];
       }
       return f;
     };
-    const double fold = fval(x);
+    const real fold = fval(x);
     bool changed = false;
-    double steplength = 1.0;
+    real steplength = 1.0;
     for (int ia = 0; ia < cfg.n_alphas; ++ia, steplength *= 0.5) {
-      for (int i = 0; i < n; ++i) xnew[i] = std::max(std::min(x[i] + steplength * dx[i], ub[i]), lb[i]);
-      const double fnew = fval(xnew);
-      double gd = 0.0;
+      for (int i = 0; i < n; ++i) xnew[i] = rmax(rmin(x[i] + steplength * dx[i], ub[i]), lb[i]);
+      const real fnew = fval(xnew);
+      real gd = 0.0;
       for (int i = 0; i < n; ++i) gd += g[i] * (x[i] - xnew[i]);
       if (fold - fnew > cfg.boxqp_th_acceptstep * gd) {
         for (int i = 0; i < n; ++i) {
@@ -879,13 +910,13 @@ void boxqp_solve(const ffmpc_config &cfg, const double H[NJ][NJ], const double *
 struct Solver {
   const Problem &P;
   int N, nx;
-  std::vector<double> xs, us, xs_try, us_try, fs;             // [(N+1)*nx], [N*7]
+  std::vector<real> xs, us, xs_try, us_try, fs;             // [(N+1)*nx], [N*7]
   std::vector<NodeData> nd;                                    // N+1 knots
-  std::vector<double> Vxx, Vx, K, k, Qu, Quuk;                  // [(N+1)*nx*nx], [(N+1)*nx], [N*7*nx], [N*7] ...
-  double cost = 0, cost_try = 0, preg, dg = 0, dq = 0, d1 = 0, d2 = 0, dV = 0, dVexp = 0, stop = 0, steplength = 1;
+  std::vector<real> Vxx, Vx, K, k, Qu, Quuk;                  // [(N+1)*nx*nx], [(N+1)*nx], [N*7*nx], [N*7] ...
+  real cost = 0, cost_try = 0, preg, dg = 0, dq = 0, d1 = 0, d2 = 0, dV = 0, dVexp = 0, stop = 0, steplength = 1;
   bool is_feasible = false, was_feasible = false;
   int iter = 0;
-  double f_pred[2][3];
+  real f_pred[2][3];
 
   explicit Solver(const Problem &p) : P(p), N(p.N), nx(p.nx) {
     xs.assign((N + 1) * nx, 0.0); xs_try = xs; fs = xs;
@@ -893,7 +924,7 @@ struct Solver {
     nd.resize(N + 1);
     Vxx.assign((N + 1) * nx * nx, 0.0); Vx.assign((N + 1) * nx, 0.0);
     K.assign(N * NJ * nx, 0.0); k.assign(N * NJ, 0.0); Qu = k; Quuk = k;
-    for (auto &r : f_pred) for (auto &v : r) v = std::numeric_limits<double>::quiet_NaN();
+    for (auto &r : f_pred) for (auto &v : r) v = rnan();
   }
 
   void record_force(int t, const NodeData &d) {
@@ -914,14 +945,14 @@ struct Solver {
       for (int i = 0; i < nx; ++i) fs[(t + 1) * nx + i] = nd[t].xnext[i] - xs[(t + 1) * nx + i];
   }
 
-  bool finite_vec(const double *v, int n) {
-    for (int i = 0; i < n; ++i) if (!std::isfinite(v[i])) return false;
+  bool finite_vec(const real *v, int n) {
+    for (int i = 0; i < n; ++i) if (!rfinite(v[i])) return false;
     return true;
   }
 
   bool backward_pass() {
     const int n = nx;
-    double *VxxN = &Vxx[N * n * n], *VxN = &Vx[N * n];
+    real *VxxN = &Vxx[N * n * n], *VxN = &Vx[N * n];
     for (int i = 0; i < n; ++i) {
       for (int j = 0; j < n; ++j) VxxN[i * n + j] = nd[N].Lxx[i][j];
       VxxN[i * n + i] += preg;
@@ -929,71 +960,71 @@ struct Solver {
     }
     if (!is_feasible)
       for (int i = 0; i < n; ++i) {
-        double s = 0.0;
+        real s = 0.0;
         for (int j = 0; j < n; ++j) s += VxxN[i * n + j] * fs[N * n + j];
         VxN[i] += s;
       }
-    std::vector<double> FxTV(n * n), Qxx(n * n), Qxu(n * NJ), FuTV(NJ * n);
+    std::vector<real> FxTV(n * n), Qxx(n * n), Qxu(n * NJ), FuTV(NJ * n);
     for (int t = N - 1; t >= 0; --t) {
       const NodeData &d = nd[t];
-      const double *Vp = &Vxx[(t + 1) * n * n], *vp = &Vx[(t + 1) * n];
-      double Quu[NJ][NJ], Qx[21], *Qu_t = &Qu[t * NJ];
+      const real *Vp = &Vxx[(t + 1) * n * n], *vp = &Vx[(t + 1) * n];
+      real Quu[NJ][NJ], Qx[21], *Qu_t = &Qu[t * NJ];
       for (int i = 0; i < n; ++i)
         for (int j = 0; j < n; ++j) {
-          double s = 0.0;
+          real s = 0.0;
           for (int l = 0; l < n; ++l) s += d.Fx[l][i] * Vp[l * n + j];
           FxTV[i * n + j] = s;
         }
       for (int i = 0; i < n; ++i) {
         for (int j = 0; j < n; ++j) {
-          double s = d.Lxx[i][j];
+          real s = d.Lxx[i][j];
           for (int l = 0; l < n; ++l) s += FxTV[i * n + l] * d.Fx[l][j];
           Qxx[i * n + j] = s;
         }
-        double s = d.Lx[i];
+        real s = d.Lx[i];
         for (int l = 0; l < n; ++l) s += d.Fx[l][i] * vp[l];
         Qx[i] = s;
       }
       for (int a = 0; a < NJ; ++a)
         for (int j = 0; j < n; ++j) {
-          double s = 0.0;
+          real s = 0.0;
           for (int l = 0; l < n; ++l) s += d.Fu[l][a] * Vp[l * n + j];
           FuTV[a * n + j] = s;
         }
       for (int i = 0; i < n; ++i)
         for (int a = 0; a < NJ; ++a) {
-          double s = d.Lxu[i][a];
+          real s = d.Lxu[i][a];
           for (int l = 0; l < n; ++l) s += FxTV[i * n + l] * d.Fu[l][a];
           Qxu[i * NJ + a] = s;
         }
       for (int a = 0; a < NJ; ++a) {
         for (int b = 0; b < NJ; ++b) {
-          double s = d.Luu[a][b];
+          real s = d.Luu[a][b];
           for (int l = 0; l < n; ++l) s += FuTV[a * n + l] * d.Fu[l][b];
           Quu[a][b] = s;
         }
         Quu[a][a] += preg;
-        double s = d.Lu[a];
+        real s = d.Lu[a];
         for (int l = 0; l < n; ++l) s += d.Fu[l][a] * vp[l];
         Qu_t[a] = s;
       }
       // computeGains
-      double *Kt = &K[t * NJ * n], *kt = &k[t * NJ];
+      real *Kt = &K[t * NJ * n], *kt = &k[t * NJ];
       const bool box = P.cfg.use_box_fddp && is_feasible;
       if (!box) {
-        double L[NJ][NJ];
+        real L[NJ][NJ];
         for (int a = 0; a < NJ; ++a) for (int b = 0; b < NJ; ++b) L[a][b] = Quu[a][b];
-        if (!chol<double, NJ>(L, NJ)) return false;
+        if (!chol<real, NJ>(L, NJ)) return false;
         for (int j = 0; j < n; ++j) {
-          double col[NJ];
+          real col[NJ];
           for (int a = 0; a < NJ; ++a) col[a] = Qxu[j * NJ + a];
-          chol_solve<double, NJ>(L, NJ, col);
+          chol_solve<real, NJ>(L, NJ, col);
           for (int a = 0; a < NJ; ++a) Kt[a * n + j] = col[a];
         }
         for (int a = 0; a < NJ; ++a) kt[a] = Qu_t[a];
-        chol_solve<double, NJ>(L, NJ, kt);
+        chol_solve<real, NJ>(L, NJ, kt);
       } else {
-        double lb[NJ], ub[NJ];
+        real lb[NJ], ub[NJ];
         for (int a = 0; a < NJ; ++a) {
           lb[a] = -P.cfg.tau_limits[a] - us[t * NJ + a];
           ub[a] = P.cfg.tau_limits[a] - us[t * NJ + a];
@@ -1001,13 +1032,13 @@ struct Solver {
         BoxQPSol s;
         boxqp_solve(P.cfg, Quu, Qu_t, lb, ub, kt, s);
         if (!s.ok) return false;
-        double Qinv[NJ][NJ];
+        real Qinv[NJ][NJ];
         for (int a = 0; a < NJ; ++a) for (int b = 0; b < NJ; ++b) Qinv[a][b] = 0.0;
         for (int i = 0; i < s.nf; ++i)
           for (int j = 0; j < s.nf; ++j) Qinv[s.free_idx[i]][s.free_idx[j]] = s.Hff_inv[i][j];
         for (int a = 0; a < NJ; ++a)
           for (int j = 0; j < n; ++j) {
-            double acc = 0.0;
+            real acc = 0.0;
             for (int b = 0; b < NJ; ++b) acc += Qinv[a][b] * Qxu[j * NJ + b];
             Kt[a * n + j] = acc;
           }
@@ -1015,32 +1046,32 @@ struct Solver {
         for (int i = 0; i < s.ncl; ++i) Qu_t[s.clamped_idx[i]] = 0.0;
       }
       // value function
-      double *Vt = &Vxx[t * n * n], *vt = &Vx[t * n], *Quuk_t = &Quuk[t * NJ];
+      real *Vt = &Vxx[t * n * n], *vt = &Vx[t * n], *Quuk_t = &Quuk[t * NJ];
       for (int a = 0; a < NJ; ++a) {
-        double s = 0.0;
+        real s = 0.0;
         for (int b = 0; b < NJ; ++b) s += Quu[a][b] * kt[b];
         Quuk_t[a] = s;
       }
       for (int i = 0; i < n; ++i) {
-        double s = Qx[i];
+        real s = Qx[i];
         for (int a = 0; a < NJ; ++a) s += Kt[a * n + i] * Quuk_t[a];
         for (int a = 0; a < NJ; ++a) s -= 2.0 * (Kt[a * n + i] * Qu_t[a]);
         vt[i] = s;
         for (int j = 0; j < n; ++j) {
-          double v = Qxx[i * n + j];
+          real v = Qxx[i * n + j];
           for (int a = 0; a < NJ; ++a) v -= Qxu[i * NJ + a] * Kt[a * n + j];
           Vt[i * n + j] = v;
         }
       }
       for (int i = 0; i < n; ++i)
         for (int j = i; j < n; ++j) {
-          const double v = 0.5 * (Vt[i * n + j] + Vt[j * n + i]);
+          const real v = 0.5 * (Vt[i * n + j] + Vt[j * n + i]);
           Vt[i * n + j] = Vt[j * n + i] = v;
         }
       for (int i = 0; i < n; ++i) Vt[i * n + i] += preg;
       if (!is_feasible)
         for (int i = 0; i < n; ++i) {
-          double s = 0.0;
+          real s = 0.0;
           for (int j = 0; j < n; ++j) s += Vt[i * n + j] * fs[t * n + j];
           vt[i] += s;
         }
@@ -1053,22 +1084,22 @@ struct Solver {
     const int n = nx;
     dg = 0.0; dq = 0.0;
     auto fVf = [&](int t) {
-      double s = 0.0;
+      real s = 0.0;
       for (int i = 0; i < n; ++i) {
-        double r = 0.0;
+        real r = 0.0;
         for (int j = 0; j < n; ++j) r += Vxx[t * n * n + i * n + j] * fs[t * n + j];
         s += fs[t * n + i] * r;
       }
       return s;
     };
     if (!is_feasible) {
-      double s = 0.0;
+      real s = 0.0;
       for (int i = 0; i < n; ++i) s += Vx[N * n + i] * fs[N * n + i];
       dg -= s;
       dq += fVf(N);
     }
     for (int t = 0; t < N; ++t) {
-      double a = 0.0, b = 0.0;
+      real a = 0.0, b = 0.0;
       for (int i = 0; i < NJ; ++i) {
         a += Qu[t * NJ + i] * k[t * NJ + i];
         b += k[t * NJ + i] * Quuk[t * NJ + i];
@@ -1076,7 +1107,7 @@ struct Solver {
       dg += a;
       dq -= b;
       if (!is_feasible) {
-        double s = 0.0;
+        real s = 0.0;
         for (int i = 0; i < n; ++i) s += Vx[t * n + i] * fs[t * n + i];
         dg -= s;
         dq += fVf(t);
@@ -1086,12 +1117,12 @@ struct Solver {
 
   void expected_improvement() {
     const int n = nx;
-    double dv = 0.0;
+    real dv = 0.0;
     if (!is_feasible) {
       auto term = [&](int t) {
-        double s = 0.0;
+        real s = 0.0;
         for (int i = 0; i < n; ++i) {
-          double r = 0.0;
+          real r = 0.0;
           for (int j = 0; j < n; ++j) r += Vxx[t * n * n + i * n + j] * (xs[t * n + j] - xs_try[t * n + j]);
           s += fs[t * n + i] * r;
         }
@@ -1105,42 +1136,42 @@ struct Solver {
   }
 
   // returns false on a NaN/inf rollout ("forward_error")
-  bool forward_pass(double alpha) {
+  bool forward_pass(real alpha) {
     const int n = nx;
     cost_try = 0.0;
-    double xnext[21];
+    real xnext[21];
     for (int i = 0; i < n; ++i) xnext[i] = P.x0[i];
     const bool close = is_feasible || alpha == 1.0;
     NodeData d;
     for (int t = 0; t < N; ++t) {
-      double *xt = &xs_try[t * n], *ut = &us_try[t * NJ];
+      real *xt = &xs_try[t * n], *ut = &us_try[t * NJ];
       for (int i = 0; i < n; ++i) xt[i] = close ? xnext[i] : xnext[i] + fs[t * n + i] * (alpha - 1.0);
       for (int a = 0; a < NJ; ++a) {
-        double s = us[t * NJ + a] - k[t * NJ + a] * alpha;
-        double kd = 0.0;
+        real s = us[t * NJ + a] - k[t * NJ + a] * alpha;
+        real kd = 0.0;
         for (int j = 0; j < n; ++j) kd += K[t * NJ * n + a * n + j] * (xt[j] - xs[t * n + j]);
         s -= kd;
-        if (P.cfg.use_box_fddp) s = std::min(std::max(s, -P.cfg.tau_limits[a]), P.cfg.tau_limits[a]);
+        if (P.cfg.use_box_fddp) s = rmin(rmax(s, -P.cfg.tau_limits[a]), P.cfg.tau_limits[a]);
         ut[a] = s;
       }
       node_eval(P, t, xt, ut, false, d);
       record_force(t, d);
       for (int i = 0; i < n; ++i) xnext[i] = d.xnext[i];
       cost_try += d.cost;
-      if (!std::isfinite(cost_try) || !finite_vec(xnext, n)) return false;
+      if (!rfinite(cost_try) || !finite_vec(xnext, n)) return false;
     }
-    double *xt = &xs_try[N * n];
+    real *xt = &xs_try[N * n];
     for (int i = 0; i < n; ++i) xt[i] = close ? xnext[i] : xnext[i] + fs[N * n + i] * (alpha - 1.0);
     node_eval(P, N, xt, nullptr, false, d);
     cost_try += d.cost;
-    if (!std::isfinite(cost_try)) return false;
+    if (!rfinite(cost_try)) return false;
     return true;
   }
 
   void increase_reg() { preg *= P.cfg.reg_incfactor; if (preg > P.cfg.reg_max) preg = P.cfg.reg_max; }
   void decrease_reg() { preg /= P.cfg.reg_decfactor; if (preg < P.cfg.reg_min) preg = P.cfg.reg_min; }
 
-  bool solve(const double *xs_init, const double *us_init, int maxiter, bool fixed_iters) {
+  bool solve(const real *xs_init, const real *us_init, int maxiter, bool fixed_iters) {
     const ffmpc_config &c = P.cfg;
     std::copy(xs_init, xs_init + (N + 1) * nx, xs.begin());
     std::copy(us_init, us_init + N * NJ, us.begin());
@@ -1162,7 +1193,7 @@ struct Solver {
       steplength = 1.0;
       g_iterations.fetch_add(1, std::memory_order_relaxed);
       for (int ia = 0; ia < c.n_alphas; ++ia) {
-        steplength = std::ldexp(1.0, -ia);
+        steplength = rldexp(1.0, -ia);
         g_rollouts.fetch_add(1, std::memory_order_relaxed);
         g_trial_hist[ia].fetch_add(1, std::memory_order_relaxed);
         if (!forward_pass(steplength)) continue;
@@ -1190,7 +1221,7 @@ struct Solver {
         increase_reg();
         if (preg == c.reg_max) return false;
       }
-      stop = std::fabs(d1 + 0.5 * d2);
+      stop = rabs(d1 + 0.5 * d2);
       if (!fixed_iters && was_feasible && stop < c.th_stop) return true;
     }
     return false;
@@ -1212,10 +1243,10 @@ void make_problem(const ffmpc_config &cfg, const ffmpc_model &mdl, const ffmpc_b
     for (int i = 0; i < NJ; ++i) P.tau_ref[i] = in.tau_ref[(size_t)b * NJ + i];
   } else {
     // _compute_tau_reference "gravity_x0": pin.rnea(q0, 0, 0)  (crocoddyl_classical.py:447-460)
-    Kin<double> k;
-    double zero[NJ] = {0, 0, 0, 0, 0, 0, 0};
-    kinematics<double>(mdl, P.x0, zero, k);
-    rnea<double>(mdl, k, zero, nullptr, P.tau_ref);
+    Kin<real> k;
+    real zero[NJ] = {0, 0, 0, 0, 0, 0, 0};
+    kinematics<real>(mdl, P.x0, zero, k);
+    rnea<real>(mdl, k, zero, nullptr, P.tau_ref);
   }
   for (int i = 0; i < 21; ++i) P.y_ref[i] = (i < P.nx) ? P.x0[i] : 0.0;  // y_ref = y0 (FF :782)
 }
@@ -1295,7 +1326,7 @@ int ffmpc_oracle_solve_batch(const ffmpc_config *cfg, const ffmpc_model *mdl, co
     Problem P;
     make_problem(*cfg, *mdl, *in, b, P);
     Solver S(P);
-    std::vector<double> xs0((N + 1) * nx), us0(N * NJ);
+    std::vector<real> xs0((N + 1) * nx), us0(N * NJ);
     if (in->xs_init) std::copy(in->xs_init + (size_t)b * (N + 1) * nx, in->xs_init + (size_t)(b + 1) * (N + 1) * nx, xs0.begin());
     else for (int t = 0; t <= N; ++t) for (int i = 0; i < nx; ++i) xs0[t * nx + i] = P.x0[i];
     if (in->us_init) std::copy(in->us_init + (size_t)b * N * NJ, in->us_init + (size_t)(b + 1) * N * NJ, us0.begin());
@@ -1334,7 +1365,10 @@ int ffmpc_oracle_node_eval(const ffmpc_config *cfg, const ffmpc_model *mdl, cons
     make_problem(*cfg, *mdl, *in, inst[m], P);
     if (knot[m] < 0 || knot[m] > P.N) { g_err = "knot out of range"; return FFMPC_ERR_ARG; }
     NodeData d;
-    node_eval(P, knot[m], x + (size_t)m * nx, u + (size_t)m * NJ, true, d);
+    real xr[21], ur[NJ];
+    for (int i = 0; i < nx; ++i) xr[i] = x[(size_t)m * nx + i];
+    for (int i = 0; i < NJ; ++i) ur[i] = u[(size_t)m * NJ + i];
+    node_eval(P, knot[m], xr, ur, true, d);
     if (out->xnext) for (int i = 0; i < nx; ++i) out->xnext[(size_t)m * nx + i] = d.xnext[i];
     if (out->cost) out->cost[m] = d.cost;
     if (out->force) for (int i = 0; i < 3; ++i) out->force[(size_t)m * 3 + i] = d.lam[i];
@@ -1366,7 +1400,10 @@ int ffmpc_oracle_node_calc(const ffmpc_config *cfg, const ffmpc_model *mdl, cons
     Problem P;
     make_problem(*cfg, *mdl, *in, inst[m], P);
     NodeData d;
-    node_eval(P, knot[m], x + (size_t)m * nx, u + (size_t)m * NJ, false, d);
+    real xr[21], ur[NJ];
+    for (int i = 0; i < nx; ++i) xr[i] = x[(size_t)m * nx + i];
+    for (int i = 0; i < NJ; ++i) ur[i] = u[(size_t)m * NJ + i];
+    node_eval(P, knot[m], xr, ur, false, d);
     if (xnext) for (int i = 0; i < nx; ++i) xnext[(size_t)m * nx + i] = d.xnext[i];
     if (cost) cost[m] = d.cost;
     if (force) for (int i = 0; i < 3; ++i) force[(size_t)m * 3 + i] = d.lam[i];

@@ -18,8 +18,10 @@ from franka_force_feedback_mpc_b200 import _abi
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libffmpc_oracle.so")
 _FAST_PATH = os.path.join(_HERE, "libffmpc_oracle_fast.so")
+_QUAD_PATH = os.path.join(_HERE, "libffmpc_oracle_quad.so")
 _lib = None
 _fast = None
+_quad = None
 
 
 def build(force: bool = False) -> str:
@@ -29,6 +31,7 @@ def build(force: bool = False) -> str:
         os.path.exists(p) and os.path.getmtime(p) > os.path.getmtime(_LIB_PATH) for p in (src, hdr)
     )
     stale = stale or not os.path.exists(_FAST_PATH) or os.path.getmtime(_FAST_PATH) < os.path.getmtime(_LIB_PATH)
+    stale = stale or not os.path.exists(_QUAD_PATH) or os.path.getmtime(_QUAD_PATH) < os.path.getmtime(_LIB_PATH)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
     return _LIB_PATH
@@ -45,6 +48,17 @@ def lib():
 
 from franka_force_feedback_mpc_b200.batch import (  # noqa: E402,F401  (shared host-side containers)
     BatchInputs, alloc_node_outputs, alloc_outputs, node_outputs_abi, outputs_abi, f64 as _f64, ptr as _ptr)
+
+
+def quad_lib():
+    """The same oracle source with every scalar in IEEE binary128 (libquadmath): the higher-precision arbiter of the
+    parity tests.  fp64 at the C boundary, ~50x slower than the fp64 build.  Use as ``solve_batch(..., _use=quad_lib())``."""
+    global _quad
+    if _quad is None:
+        build()
+        _quad = C.CDLL(_QUAD_PATH)
+        _quad.ffmpc_oracle_last_error.restype = C.c_char_p
+    return _quad
 
 
 def _cpu_has(*flags) -> bool:
@@ -92,7 +106,7 @@ def solve_batch(cfg: _abi.Config, model: _abi.Model, inp: BatchInputs, max_iters
     return out
 
 
-def node_eval(cfg: _abi.Config, model: _abi.Model, inp: BatchInputs, inst, knot, x, u) -> dict:
+def node_eval(cfg: _abi.Config, model: _abi.Model, inp: BatchInputs, inst, knot, x, u, _use=None) -> dict:
     inst = np.ascontiguousarray(inst, dtype=np.int32)
     knot = np.ascontiguousarray(knot, dtype=np.int32)
     M = inst.size
@@ -100,7 +114,7 @@ def node_eval(cfg: _abi.Config, model: _abi.Model, inp: BatchInputs, inst, knot,
     u = _f64(u, (M, 7))
     out = alloc_node_outputs(M, inp.nx)
     s_in, s_out = inp.to_abi(), node_outputs_abi(out)
-    _check(lib().ffmpc_oracle_node_eval(C.byref(cfg), C.byref(model), C.byref(s_in), M, _ptr(inst), _ptr(knot),
+    _check((_use or lib()).ffmpc_oracle_node_eval(C.byref(cfg), C.byref(model), C.byref(s_in), M, _ptr(inst), _ptr(knot),
                                         _ptr(x), _ptr(u), C.byref(s_out)))
     return out
 

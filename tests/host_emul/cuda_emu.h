@@ -261,6 +261,8 @@ inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); retur
 inline cudaError_t cudaStreamCreate(cudaStream_t *s) { *s = nullptr; return 0; }
 constexpr unsigned cudaStreamNonBlocking = 1u, cudaEventDisableTiming = 2u;
 inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned) { *s = (cudaStream_t)(void *)1; return 0; }  // non-null: "created"
+inline cudaError_t cudaStreamCreateWithPriority(cudaStream_t *s, unsigned, int) { *s = (cudaStream_t)(void *)1; return 0; }
+inline cudaError_t cudaDeviceGetStreamPriorityRange(int *least, int *greatest) { *least = 0; *greatest = -5; return 0; }
 inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0) { return 0; }
 inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }

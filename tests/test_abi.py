@@ -37,7 +37,7 @@ def test_ctypes_mirror_matches_compiled_structs(built):
     from franka_force_feedback_mpc_b200 import _abi, engine
 
     lib = engine.load_library()
-    sizes = (C.c_int * 8)()
+    sizes = (C.c_int * 10)()
     lib.ffmpc_abi_sizes(sizes)
     assert sizes[0] == C.sizeof(_abi.Model)
     assert sizes[1] == C.sizeof(_abi.Config)
@@ -47,6 +47,8 @@ def test_ctypes_mirror_matches_compiled_structs(built):
     assert sizes[5] == C.sizeof(_abi.TickPolicy)
     assert sizes[6] == C.sizeof(_abi.TickIn)
     assert sizes[7] == C.sizeof(_abi.TickOut)
+    assert sizes[8] == C.sizeof(_abi.Options)
+    assert sizes[9] == C.sizeof(_abi.Info)
 
 
 def test_default_config_matches_oracle_default(built, orc):

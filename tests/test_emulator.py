@@ -138,14 +138,14 @@ def test_emulated_friction_cone_matches_oracle(emu, orc, ff):
 
 def test_emulated_host_call_split_is_bitwise_neutral(emu):
     """ffmpc_solve_batch_host solves large batches in chunks so that a chunk's device->host copies overlap the next
-    chunk's solve (ffmpc_options.host_chunks): the outputs must not depend on the split (mixed modes, so that the mode
+    chunk's solve (ffmpc_options.sub_batches): the outputs must not depend on the split (mixed modes, so that the mode
     buckets of the chunks differ from those of the whole batch)."""
     B, N = 20, 8
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.6)
-    eng = _engine(emu, cfg, am, B, host_chunks=1)
+    eng = _engine(emu, cfg, am, B, sub_batches=1)
     whole = eng.solve_host(inp, 4, True)
     eng.close()
-    eng = _engine(emu, cfg, am, B, host_chunks=3)      # 20 instances -> 7 + 7 + 6
+    eng = _engine(emu, cfg, am, B, sub_batches=3)      # 20 instances -> 7 + 7 + 6
     split = eng.solve_host(inp, 4, True)
     eng.close()
     for k in whole:

@@ -331,13 +331,13 @@ def test_friction_cone_point3d_matches_oracle(built, orc, ff):
 
 def test_host_call_split_is_bitwise_neutral(built):
     """ffmpc_solve_batch_host overlaps the device->host copies of a chunk with the solve of the next one
-    (ffmpc_options.host_chunks): outputs must be bit-identical to the unsplit call."""
+    (ffmpc_options.sub_batches): outputs must be bit-identical to the unsplit call."""
     B, N = 2048, 50
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.75)
-    eng = _eng(cfg, am, B, host_chunks=1)
+    eng = _eng(cfg, am, B, sub_batches=1)
     whole = eng.solve_host(inp, 5, True)
     eng.close()
-    eng = _eng(cfg, am, B, host_chunks=5)   # 2048 -> 410 x 4 + 408
+    eng = _eng(cfg, am, B, sub_batches=5)   # 2048 -> 410 x 4 + 408
     split = eng.solve_host(inp, 5, True)
     eng.close()
     for k in whole:
