@@ -171,6 +171,51 @@ def benchmark_ff_config(**over) -> ForceFeedbackMPCConfig:
     return ForceFeedbackMPCConfig(**kw)
 
 
+def dev_classical_config(**over) -> ClassicalMPCConfig:
+    """The development (non-benchmark) preset of src/run/run_classical.py:316-361."""
+    kw = dict(
+        horizon=50, dt=0.005, dt_ocp=0.01, z_contact=0.342, z_press=0.0075, w_ee_pos=1.3e3, w_ee_ori=6.0e1,
+        ori_weights=np.array([2.4, 2.4, 0.2]), w_posture=1.5e-1, w_v=8.0e-2, posture_ref_mode="q_nom", w_tau=2.0e-3,
+        torque_ref_mode="gravity_x0", w_tau_soft_limits=4.0, w_q_soft_limits=10.0, q_soft_limit_margin=0.10,
+        w_tau_smooth=5.0e-2, w_tangent_pos=3.5e3, w_tangent_vel=1.3e3, w_plane_z=6.0e2, w_vz=2.5e2, w_friction_cone=0.0,
+        w_unilateral=4.0e1, mu=1.0, contact_gains=np.array([150.0, 85.0]), fn_des=30.0, w_fn=5.5e1, w_wdamp=8.0e1,
+        w_wdamp_weights=np.array([2.0, 2.0, 0.3]), fn_contact_on=1.0, fn_contact_off=0.05, z_contact_band=0.012,
+        max_iters=10, mpc_update_steps=1, use_feedback_policy=True, feedback_gain_scale=0.60, max_tau_raw_inf=2.0e2,
+        contact_release_steps=80, contact_model="normal_1d", phase_source="trajectory", apply_command_filter=False,
+        strict_force_residual_dim=True, debug_every=100,
+    )
+    kw.update(over)
+    return ClassicalMPCConfig(**kw)
+
+
+def dev_ff_config(**over) -> ForceFeedbackMPCConfig:
+    """The development (non-benchmark) preset of src/run/run_force_feedback.py:331-387."""
+    kw = dict(
+        horizon=50, dt=0.005, dt_ocp=0.01, z_contact=0.342, z_press=0.0080, w_ee_pos=1.8e3, w_ee_ori=5.5e1,
+        ori_weights=np.array([2.4, 2.4, 0.2]), w_posture=6.0e-2, w_v=2.0e-2, posture_ref_mode="q_nom", w_tau=2.0e-3,
+        w_w=3.0e-4, w_w_soft_limits=3.0, w_y=5.0e-4, y_q_weights=np.array([0.2] * 4 + [0.1] * 3),
+        y_v_weights=np.array([0.08] * 4 + [0.05] * 3), y_tau_weights=np.array([0.10] * 4 + [0.06] * 3),
+        use_inner_state_reg=True, use_inner_tau_reg=True, torque_ref_mode="gravity_x0", w_tau_soft_limits=1.5,
+        w_q_soft_limits=10.0, q_soft_limit_margin=0.10, w_tau_smooth=5.0e-2, w_tangent_pos=4.8e3, w_tangent_vel=1.9e3,
+        w_plane_z=5.0e2, w_vz=2.0e2, w_friction_cone=0.0, w_unilateral=3.0e1, mu=1.0,
+        contact_gains=np.array([150.0, 90.0]), fn_des=26.0, w_fn=4.0e1, w_wdamp=8.0e1,
+        w_wdamp_weights=np.array([2.0, 2.0, 0.3]), fn_contact_on=1.0, fn_contact_off=0.05, z_contact_band=0.012,
+        max_iters=10, mpc_update_steps=1, use_feedback_policy=True, feedback_gain_scale=0.60, max_tau_raw_inf=2.2e2,
+        contact_release_steps=80, contact_model="normal_1d", phase_source="trajectory", apply_command_filter=False,
+        strict_force_residual_dim=True, ff_tau_state_source="tau_meas_act_filt", ff_cutoff_hz=90.0,
+        ff_inverse_actuation_model=True, debug_every=500,
+    )
+    kw.update(over)
+    return ForceFeedbackMPCConfig(**kw)
+
+
+PRESETS = {
+    ("benchmark", False): benchmark_classical_config, ("benchmark", True): benchmark_ff_config,
+    ("dev", False): dev_classical_config, ("dev", True): dev_ff_config,
+    ("defaults", False): ClassicalMPCConfig, ("defaults", True): ForceFeedbackMPCConfig,   # the dataclass defaults
+}
+
+
 # ------------------------------------------------------------------------------------------------
 # lowering to the C struct
 # ------------------------------------------------------------------------------------------------

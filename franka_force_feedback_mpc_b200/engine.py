@@ -144,9 +144,11 @@ class FFMPCEngine:
         for name in OUTPUT_NAMES:
             t = t_out.get(name)
             setattr(s_out, name, None if t is None else t.data_ptr())
-        sp = None
-        if stream is not None:
-            sp = C.c_void_p(stream.cuda_stream)
+        if stream is None:
+            # order the solve against the producers / consumers of these tensors: torch's current stream on their device
+            # (a NULL stream would mean the handle's own stream, ffmpc.h)
+            stream = torch.cuda.current_stream(dev)
+        sp = C.c_void_p(stream.cuda_stream)
         self._check(self.lib.ffmpc_solve_batch(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out), sp))
         return t_out
 

@@ -389,29 +389,46 @@ def run_closed_loops(eng, cfg, plant, traj, scenarios: Sequence[str], steps: int
     `plant`: B plants behind one object -- `.dt`, `.observe() -> dict` and `.step(tau_applied[B,7]) -> dict` with
     [B, ...] arrays `q, dq, tau_bias, ee_pos, ee_vel, fn_meas` plus whatever torque channels the FF state source
     reads (MuJoCo is unavailable on this box; tests use a kinematic stand-in).  `traj(t[B]) -> (p_mj, v_mj, surf)` is
-    `synthetic.ApproachThenCircle`.  All loops of one call share one injector kind (see `injector_for_scenarios`)."""
-    from . import config as _config
-    from .synthetic import refs_pin
+    `synthetic.ApproachThenCircle`.  All loops of one call share one injector kind (see `injector_for_scenarios`).
 
+    Same OCP as the B = 1 controller mirror: `posture_ref_mode` and `torque_ref_mode` are resolved per tick into the
+    tick's x_reg_ref / tau_ref inputs; the surface latch sees what the controller sees (the injector-delayed
+    observation).  `mpc_update_steps` must be 1 (the device tick solves on every tick; every preset of the reference
+    uses 1).  The logged `fn_pred` is the RAW prediction: the reference's FF controller additionally passes it through
+    its lag/affine alignment filter for logging only (`_align_logged_force_prediction`); that filter lives in the
+    B = 1 mirror (controllers.py), not here."""
+    from . import config as _config
+    from .synthetic import batched_gravity_torque, refs_pin
+
+    if int(cfg.mpc_update_steps) != 1:
+        raise ValueError("run_closed_loops: the device tick solves on every tick; mpc_update_steps must be 1")
     B = len(scenarios)
     inj = injector_for_scenarios(scenarios, plant.dt, seeds, getattr(plant, "tau_meas_lpf_alpha", 0.2)) if benchmark_mode else None
     pol = _config.tick_policy(cfg, dt_mpc=plant.dt)
     latch = BatchedSurfaceLatch(B, cfg)
     force_latch = str(cfg.phase_source).strip().lower() == "force_latch"
     x_reg = np.concatenate([np.broadcast_to(np.asarray(q_nom, float), (B, 7)), np.zeros((B, 7))], axis=1)
-    N, dt_ocp = int(cfg.horizon), float(cfg.dt_ocp)
+    N, dt_ocp = int(cfg.horizon), _config.dt_ocp_of(cfg)
+    tmode = str(cfg.torque_ref_mode).strip().lower()
+    tau_ref = None                                       # "gravity_x0": g(q_now), evaluated on the device
+    if tmode == "zero":
+        tau_ref = np.zeros((B, 7))
+    elif tmode == "gravity_qnom":
+        tau_ref = np.repeat(batched_gravity_torque(getattr(plant, "m", None) or plant.model, np.asarray(q_nom, float)[None]), B, axis=0)
     obs = plant.observe()
     cols = {k: [] for k in ("t", "err_tan", "err_3d", "fn_meas", "fn_pred", "contact")}
+    ctl_hist = {k: [] for k in ("tau_cmd", "solver_cost", "solver_iters")}   # what the controllers did, per tick
     t = 0.0
     for k in range(int(steps)):
         seen = inj.observation_for_controller(**{n: v for n, v in obs.items() if isinstance(v, np.ndarray) and v.ndim >= 1}) if inj else obs
         _, _, hint = traj(np.full(B, t))
-        mode = latch.update(obs["fn_meas"], np.asarray(seen["ee_pos"])[:, 2], hint) if force_latch else np.asarray(hint, dtype=bool)
+        # the latch reads the controller's view of the force (obs.f_contact_normal after the injector's delay)
+        mode = latch.update(seen.get("fn_meas", obs["fn_meas"]), np.asarray(seen["ee_pos"])[:, 2], hint) if force_latch else np.asarray(hint, dtype=bool)
         x_now = np.concatenate([seen["q"], seen["dq"]] + ([torque_state(seen, cfg)] if ff else []), axis=1)
         p_ref, v_ref = refs_pin(traj, np.full(B, t), N, dt_ocp)
         x_reg_k = x_reg if str(cfg.posture_ref_mode).strip().lower() == "q_nom" else x_now[:, :14]
         out = eng.tick_host(mode.astype(np.int32), x_now, p_ref, v_ref, x_reg_k, seen["tau_bias"], pol, int(cfg.max_iters),
-                            fixed_iters=fixed_iters, reset=(k == 0))
+                            fixed_iters=fixed_iters, reset=(k == 0), tau_ref=tau_ref)
         tau_applied = plant_command(out["tau_cmd"], scenarios, inj)
         obs = plant.step(tau_applied)
         t += plant.dt
@@ -421,6 +438,9 @@ def run_closed_loops(eng, cfg, plant, traj, scenarios: Sequence[str], steps: int
                    fn_pred=out["fn_pred"], contact=(np.asarray(obs["fn_meas"]) > contact_threshold).astype(np.int64))
         for n, v in row.items():
             cols[n].append(np.broadcast_to(np.asarray(v, dtype=float), (B,)).copy())
+        ctl_hist["tau_cmd"].append(out["tau_cmd"].copy())
+        ctl_hist["solver_cost"].append(out["cost"].copy())
+        ctl_hist["solver_iters"].append(out["iters"].copy())
         if log is not None:
             log.log(**row, ee_pos=obs["ee_pos"], ee_ref=p_next, ee_vel=obs["ee_vel"], ee_vel_ref=v_next, fn_des=float(cfg.fn_des),
                     tau_cmd=out["tau_cmd"], tau_applied=tau_applied, surface_ref=np.asarray(surf_next).astype(np.int64),
@@ -440,4 +460,4 @@ def run_closed_loops(eng, cfg, plant, traj, scenarios: Sequence[str], steps: int
         log.set_meta_rows(**metrics)
         log.set_meta(contact_phase_start_s=float(t_contact_phase))
         log.save()
-    return dict(hist, **metrics)
+    return dict(hist, **metrics, **{n: np.stack(v, axis=1) for n, v in ctl_hist.items()})

@@ -44,43 +44,49 @@ def shard_inputs(inp: BatchInputs, world: int, rank: int) -> BatchInputs:
     return inp.slice(np.arange(lo, hi))
 
 
-def gather_results(local: Dict[str, np.ndarray], total: int, world: int, rank: int, names: Optional[Sequence[str]] = None,
-                   dist=None, device=None) -> Optional[Dict[str, np.ndarray]]:
-    """Gather per-instance results of every rank onto rank 0 in instance order.
+def gather_results(local: Dict[str, object], total: int, world: int, rank: int, names: Optional[Sequence[str]] = None,
+                   dist=None, device=None, to_numpy: bool = True):
+    """Gather per-instance results of every rank in instance order (north_star: "only a final result gather over NVLink").
 
-    `local[name]` has leading dimension = this rank's shard size.  Uses all_gather on tensors padded to the
-    largest shard (works for both gloo and nccl; no data-path collective ever precedes this call).
-    Returns the full arrays on rank 0 and None elsewhere.  `dist=None` (single process) returns `local`.
-    """
+    `local[name]`: numpy array or torch tensor whose leading dimension is this rank's shard size.  Torch tensors stay
+    where they are: a CUDA tensor is padded to the largest shard ON ITS DEVICE and all-gathered by NCCL from device memory
+    (no host round trip); numpy arrays go through `device` (None: CPU tensors, the gloo test path).  No data-path
+    collective ever precedes this call.  Rank 0 gets the full arrays (numpy when `to_numpy`, else torch tensors on the
+    gathering device), the other ranks None.  `dist=None` (single process) returns `local`."""
     names = list(names if names is not None else local.keys())
     if world == 1 or dist is None:
-        return {n: np.asarray(local[n]) for n in names}
+        return {n: (np.asarray(local[n].cpu() if hasattr(local[n], "cpu") else local[n]) if to_numpy else local[n]) for n in names}
     import torch
 
     sizes = shard_sizes(total, world)
     cap = int(sizes.max())
     out = {} if rank == 0 else None
     for n in names:
-        a = np.ascontiguousarray(local[n])
-        if a.shape[0] != sizes[rank]:
-            raise ValueError(f"{n}: leading dimension {a.shape[0]} != shard size {sizes[rank]}")
-        pad = np.zeros((cap,) + a.shape[1:], dtype=a.dtype)
-        pad[: a.shape[0]] = a
-        t = torch.from_numpy(pad)
-        if device is not None:
+        a = local[n]
+        t = a if torch.is_tensor(a) else torch.from_numpy(np.ascontiguousarray(a))
+        if device is not None and t.device != torch.device(device):
             t = t.to(device)
+        if t.shape[0] != sizes[rank]:
+            raise ValueError(f"{n}: leading dimension {t.shape[0]} != shard size {sizes[rank]}")
+        if t.shape[0] != cap:
+            pad = torch.zeros((cap,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            pad[: t.shape[0]] = t
+            t = pad
+        t = t.contiguous()
         bufs = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(bufs, t)
         if rank == 0:
-            out[n] = np.concatenate([bufs[r][: int(sizes[r])].cpu().numpy() for r in range(world)], axis=0)
+            full = torch.cat([bufs[r][: int(sizes[r])] for r in range(world)], dim=0)
+            out[n] = full.cpu().numpy() if to_numpy else full
     return out
 
 
 def solve_sharded(inp: BatchInputs, world: int, rank: int, solve: Callable[[BatchInputs], Dict[str, np.ndarray]],
                   names: Sequence[str] = ("cost", "iters", "ok", "f_pred"), dist=None, device=None):
-    """Slice -> local solve (`solve` = e.g. ``lambda s: engine.solve_host(s, iters)``) -> gather on rank 0."""
+    """Slice -> local solve (`solve` = e.g. ``lambda s: engine.solve_host(s, iters)``) -> gather on rank 0.
+    Every rank checks the WHOLE partition before anybody solves or enters the collective: a rank raising alone on its
+    empty shard would leave the others waiting in all_gather."""
+    if inp.B < world:
+        raise ValueError(f"{inp.B} instances over {world} ranks: some rank would get an empty shard")
     shard = shard_inputs(inp, world, rank)
-    local = solve(shard) if shard.B > 0 else {}
-    if shard.B == 0:
-        raise ValueError("empty shard: fewer instances than ranks")
-    return gather_results(local, inp.B, world, rank, names, dist=dist, device=device)
+    return gather_results(solve(shard), inp.B, world, rank, names, dist=dist, device=device)

@@ -9,7 +9,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from ffmpc_cases import make_case, rel_err
+from ffmpc_cases import CONFIG_CASES, make_case, rel_err, run_config_case
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 EMU_DIR = os.path.join(HERE, "host_emul")
@@ -150,3 +150,12 @@ def test_emulated_host_call_split_is_bitwise_neutral(emu):
     eng.close()
     for k in whole:
         assert np.array_equal(whole[k], split[k], equal_nan=True), k
+
+
+@pytest.mark.parametrize("case", CONFIG_CASES, ids=[c[0] for c in CONFIG_CASES])
+def test_emulated_configuration_matches_oracle(emu, orc, case):
+    """tests/test_gpu_configs.py at a small size on the emulator build: inner-regularisation flags, reference modes,
+    development presets, dataclass defaults, benchmark horizons."""
+    name, ff, nc, cf, horizon, kw = case
+    small = (name, ff, nc, cf, 6 if horizon else None, kw)   # the horizon cases only differ by N: keep them cheap here
+    run_config_case(lambda cfg, am, B: _engine(emu, cfg, am, B), orc, small, B=3, N=6, iters=2)

@@ -224,6 +224,115 @@ class KinematicPlants:
         return self.observe()
 
 
+class TorqueDrivenPlants(KinematicPlants):
+    """Stand-in plants that RESPOND to the applied torque, so that the loop is closed (the MuJoCo plant is unavailable on
+    this box): decoupled joints with inertia I and viscous damping, qdd = (tau - g(q) - D dq) / I, semi-implicit Euler;
+    the 'contact force' is the spring on table penetration of the parent class."""
+
+    I = np.array([2.0, 2.0, 2.0, 2.0, 0.5, 0.5, 0.5])
+    D = 8.0 * I
+
+    def step(self, tau_applied):
+        self.k += 1
+        g = self.syn.batched_gravity_torque(self.m, self.q)
+        self.dq = self.dq + self.dt * (np.asarray(tau_applied, float) - g - self.D * self.dq) / self.I
+        self.q = self.q + self.dt * self.dq
+        self.tau = np.array(tau_applied, float)
+        return self.observe()
+
+
+def _reference_loops(cfg, plant, traj, scen, steps, ff, benchmark_mode, q_nom, t_contact_phase=0.8, contact_threshold=0.5):
+    """The loop of `scenarios.run_closed_loops` with the device tick replaced by B INDEPENDENT controller mirrors
+    (controllers.py, pinned to the reference's own methods by tests/test_controllers.py), each solving its B = 1 problem
+    with the CPU oracle: nothing of the engine on this side."""
+    import types
+
+    from franka_force_feedback_mpc_b200 import controllers
+    from test_controllers import FakeSim
+    from test_tick import OracleB1Solver
+
+    B = len(scen)
+    inj = sc.injector_for_scenarios(scen, plant.dt, None, 0.2) if benchmark_mode else None
+    ctls = []
+    for b in range(B):
+        sim = FakeSim(plant.m, np.array(q_nom, float))   # nominal pose / frame offsets of the controller constructor
+        sim.dt = plant.dt
+        ctl = getattr(controllers, "ForceFeedbackCrocoddylMPC" if ff else "ClassicalCrocoddylMPC")(sim, lambda t: traj(t), config=cfg)
+        ctl._solver = OracleB1Solver(*ctl._abi())
+        ctls.append(ctl)
+    obs = plant.observe()
+    for b, ctl in enumerate(ctls):
+        # the reference builds each controller on ITS plant: the last-command memory starts at that plant's gravity torque
+        # (crocoddyl_classical.py:176-178); the mirrors above were built on the nominal pose
+        ctl._tau_prev = np.array(obs["tau_bias"][b], float)
+    cols = {k: [] for k in ("t", "err_tan", "err_3d", "fn_meas", "contact", "tau_cmd", "solver_cost", "solver_iters")}
+    t = 0.0
+    for k in range(steps):
+        seen = inj.observation_for_controller(**{n: v for n, v in obs.items() if isinstance(v, np.ndarray) and v.ndim >= 1}) if inj else obs
+        taus, costs, its = [], [], []
+        for b, ctl in enumerate(ctls):
+            o = types.SimpleNamespace(**{n: np.asarray(v)[b] for n, v in seen.items()})
+            o.f_contact_normal = float(np.asarray(seen["fn_meas"])[b])
+            o.ee_quat = np.array([0.0, 1.0, 0.0, 0.0])
+            taus.append(ctl.compute_control(o, t))
+            costs.append(ctl.last_info["cost"])
+            its.append(ctl.last_info["iters"])
+        tau_cmd = np.stack(taus)
+        obs = plant.step(sc.plant_command(tau_cmd, scen, inj))
+        t += plant.dt
+        p_next, _, _ = traj(np.full(B, t))
+        err = obs["ee_pos"] - p_next
+        row = dict(t=np.full(B, t), err_tan=np.linalg.norm(err[:, :2], axis=1), err_3d=np.linalg.norm(err, axis=1), fn_meas=np.asarray(obs["fn_meas"], float),
+                   contact=(np.asarray(obs["fn_meas"]) > contact_threshold).astype(float), tau_cmd=tau_cmd, solver_cost=np.array(costs), solver_iters=np.array(its))
+        for n, v in row.items():
+            cols[n].append(np.asarray(v, float))
+    hist = {n: np.stack(v, axis=1) for n, v in cols.items()}
+    return dict(hist, **sc.closed_loop_metrics(hist["t"], hist["err_tan"], hist["err_3d"], hist["fn_meas"], hist["contact"], float(cfg.fn_des), t_contact_phase))
+
+
+METRIC_KEYS = ("rms_tangential_error", "rms_3d_error", "mean_abs_force_error", "max_normal_force", "contact_loss_pct")
+
+
+def _closed_loop_parity(lib, ff, scen, benchmark_mode, steps, N, iters, t_contact_phase):
+    """(engine sweep, oracle-mirror sweep) of the same closed loops on torque-driven stand-in plants."""
+    from franka_force_feedback_mpc_b200 import config, engine, panda, synthetic
+
+    m = panda.default_model()
+    cfg = (config.benchmark_ff_config if ff else config.benchmark_classical_config)(horizon=N, max_iters=iters)
+    traj = synthetic.benchmark_trajectory(m)
+    B = len(scen)
+    q0 = panda.Q_NEUTRAL[None] + np.random.default_rng(1).normal(0, 0.02, (B, 7))
+    from franka_force_feedback_mpc_b200 import controllers
+    from test_controllers import FakeSim
+
+    tmpl = getattr(controllers, "ForceFeedbackCrocoddylMPC" if ff else "ClassicalCrocoddylMPC")(FakeSim(m, panda.Q_NEUTRAL), lambda t: traj(t), config=cfg,
+                                                                                                 solver=object())
+    eng = engine.FFMPCEngine(*tmpl._abi(), device=0, max_batch=B, _lib=lib)   # the very config the mirrors lower to the ABI
+    got = sc.run_closed_loops(eng, cfg, TorqueDrivenPlants(m, q0), traj, scen, steps, ff=ff, q_nom=panda.Q_NEUTRAL, benchmark_mode=benchmark_mode,
+                              t_contact_phase=t_contact_phase)
+    eng.close()
+    want = _reference_loops(cfg, TorqueDrivenPlants(m, q0), traj, scen, steps, ff, benchmark_mode, panda.Q_NEUTRAL, t_contact_phase=t_contact_phase)
+    return got, want
+
+
+def _assert_closed_loop_parity(got, want, label):
+    assert np.array_equal(got["solver_iters"], want["solver_iters"]), label
+    assert np.abs(got["tau_cmd"] - want["tau_cmd"]).max() < 1e-5, (label, "tau_cmd", float(np.abs(got["tau_cmd"] - want["tau_cmd"]).max()))
+    for k in ("err_tan", "err_3d", "fn_meas"):
+        assert np.abs(got[k] - want[k]).max() <= 1e-7 * max(1.0, np.abs(want[k]).max()), (label, k)
+    assert np.array_equal(got["contact"], want["contact"]), label
+    for k in sc_metric_keys(got):
+        a, b = np.asarray(got[k], float), np.asarray(want[k], float)
+        assert np.array_equal(np.isnan(a), np.isnan(b)), (label, k)
+        ok = ~np.isnan(b)
+        assert np.all(np.abs(a[ok] - b[ok]) <= 1e-6 * np.maximum(1.0, np.abs(b[ok]))), (label, k, a, b)
+
+
+def sc_metric_keys(res):
+    """the summary-metric entries of a sweep result (run_classical.py:513-534): everything that is one number per loop"""
+    return [k for k, v in res.items() if np.asarray(v).ndim == 1 and k not in ("t",)]
+
+
 def _sweep(lib, tmp_path, ff, scen, benchmark_mode, steps=4):
     from franka_force_feedback_mpc_b200 import config, engine, panda, synthetic
 
@@ -282,3 +391,37 @@ def test_gpu_sweep_of_all_scenarios(built, tmp_path):
         assert (z["solver_iters"] >= 1).all() and np.isfinite(z["solver_cost"]).all()
     res, log = _sweep(lib, tmp_path / "bm", True, ["actuation_uncertainty"] * 8, benchmark_mode=True, steps=6)
     assert np.isfinite(res["err_3d"]).all()
+
+
+@pytest.mark.parametrize("ff,benchmark_mode", [(False, False), (True, True)])
+def test_emulated_closed_loop_matches_oracle_backed_mirrors(ff, benchmark_mode):
+    """north_star: closed-loop metrics (tangential / 3D tracking error, force error, max normal force, contact-loss %)
+    must match the reference's.  The MuJoCo plant is unavailable on this box; what CAN be checked is that the batched
+    closed loop around the device tick reproduces, tick by tick and in the end-of-run metrics, the same loops run by B
+    independent controller mirrors whose solves are answered by the CPU oracle, on stand-in plants that respond to the
+    commanded torque.  Emulator build of the kernels, small sizes; the GPU version runs all five scenarios."""
+    import subprocess
+
+    from franka_force_feedback_mpc_b200 import engine
+
+    emu_dir = os.path.join(HERE, "host_emul")
+    subprocess.check_call(["make", "-C", emu_dir, "all"], stdout=subprocess.DEVNULL)
+    lib = engine.load_library(os.path.join(emu_dir, "libffmpc_emu.so"))
+    scen = ["actuation_uncertainty"] * 2 if benchmark_mode else ["flat", "tilted_10", "actuation_uncertainty"]
+    got, want = _closed_loop_parity(lib, ff, scen, benchmark_mode, steps=5, N=6, iters=2, t_contact_phase=0.0)
+    _assert_closed_loop_parity(got, want, (ff, benchmark_mode))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ff", [False, True])
+def test_gpu_closed_loop_metrics_match_oracle_backed_mirrors(built, ff):
+    """All five scenarios x 2 loops on the real engine against the oracle-backed mirrors (see the emulator test above):
+    per-tick commands, error histories and the runner's end-of-run metrics."""
+    from franka_force_feedback_mpc_b200 import engine
+
+    lib = engine.load_library()
+    scen = [s for s in sc.SCENARIOS for _ in range(2)]
+    got, want = _closed_loop_parity(lib, ff, scen, False, steps=12, N=30, iters=5, t_contact_phase=0.0)
+    _assert_closed_loop_parity(got, want, (ff, "plain"))
+    got, want = _closed_loop_parity(lib, ff, ["actuation_uncertainty"] * 4, True, steps=12, N=30, iters=5, t_contact_phase=0.0)
+    _assert_closed_loop_parity(got, want, (ff, "benchmark"))

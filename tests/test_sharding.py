@@ -59,6 +59,20 @@ def _worker(rank: int, world: int, port: int, q):
             q.put({k: v for k, v in res.items()})
         else:
             assert res is None
+        # torch tensors in (the device-resident form of the gather; CPU tensors under gloo), torch tensors out
+        import torch
+
+        from franka_force_feedback_mpc_b200.sharding import gather_results, shard_inputs
+        loc = orc.solve_batch(cfg, am, shard_inputs(inp, world, rank), 3, True, nthreads=1)
+        tt = gather_results({k: torch.from_numpy(loc[k]) for k in ("cost", "iters")}, inp.B, world, rank, dist=dist, to_numpy=False)
+        if rank == 0:
+            assert torch.is_tensor(tt["cost"]) and np.array_equal(tt["cost"].numpy(), res["cost"]) and np.array_equal(tt["iters"].numpy(), res["iters"])
+        # fewer instances than ranks: EVERY rank raises before any collective (no deadlock)
+        try:
+            solve_sharded(inp.slice(np.arange(1)), world, rank, lambda s: {}, names, dist=dist)
+            raise AssertionError("expected ValueError")
+        except ValueError:
+            pass
         dist.barrier()
     finally:
         dist.destroy_process_group()
