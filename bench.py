@@ -81,6 +81,8 @@ def parse_args():
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
     ap.add_argument("--sub-batches", type=int, default=0, help="ffmpc_options.sub_batches (0 = auto)")
+    ap.add_argument("--tick-stream-ticks", type=int, default=600, help="ticks of the B = 1 latency streams (configs 1, 2)")
+    ap.add_argument("--no-also", action="store_true", help="skip the short BASELINE config 3 / config 5 runs")
     a = ap.parse_args()
     a.n_alphas_report = 10
     return a
@@ -230,6 +232,39 @@ def run_reference(args, rank: int, world: int):
     print(json.dumps(line), flush=True)
 
 
+def short_run(base_args, local_rank: int, variant: str, contact_model: str, B: int, iters: int, cf: float, steps: int = 2) -> dict:
+    """A short device-timed run of another BASELINE configuration (same engine, same timing method), for the `also` key."""
+    import argparse as _ap
+
+    import torch
+
+    from franka_force_feedback_mpc_b200 import engine
+
+    a = _ap.Namespace(**vars(base_args))
+    a.variant, a.contact_model, a.batch, a.iters, a.contact_fraction = variant, contact_model, B, iters, cf
+    cfg, model, inp, nx = make_problem(a, 0, B)
+    dev = torch.device("cuda", local_rank)
+    N = a.horizon
+    eng = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=B, sub_batches=a.sub_batches)
+    t_in = {k: torch.from_numpy(getattr(inp, k)).to(dev) for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+    shapes = dict(xs=(B, N + 1, nx), us=(B, N, 7), K=(B, N, 7, nx), k=(B, N, 7), cost=(B,), iters=(B,), ok=(B,))
+    t_out = {n: torch.empty(shapes[n], device=dev, dtype=torch.int32 if n in ("iters", "ok") else torch.float64) for n in shapes}
+    st = torch.cuda.Stream(device=dev)
+    for _ in range(3):
+        eng.solve_device(t_in, iters, True, t_out=t_out, stream=st)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(steps):
+        eng.solve_device(t_in, iters, True, t_out=t_out, stream=st)
+    e1.record(st)
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    ok = bool((t_out["iters"] == iters).all().item()) and bool(torch.isfinite(t_out["cost"]).all().item())
+    eng.close()
+    return {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps, "config": workload_config(a, B, nx), "all_iters_ran": ok}
+
+
 def workload_config(args, B: int, nx: int) -> dict:
     if args.variant == "ff" and args.contact_model == "normal_1d":
         which = "BASELINE config 4"                                   # the configuration the metric is quoted on (default)
@@ -318,16 +353,18 @@ def main():
     ms_total = ev0.elapsed_time(ev1)
     launches_per_step = int(eng.last_timing()[1])
     clk = clocks.stop() if rank == 0 else None
-    # kernel-family split: ONE extra, untimed step with an event after every family.  That step runs its sub-batches one
-    # after another on one stream (a per-family timeline needs it), so its families add up to MORE than ms_per_step of the
-    # timed steps, whose sub-batches overlap; the shares are what this step is for.
-    eng.set_profiling(True)
-    step_device()
+    # kernel-family split: untimed, on a second handle WITHOUT sub-batches (one stream, an event after every kernel family).
+    # The timed steps above overlap their sub-batches, so these family times add up to a little more than ms_per_step;
+    # they say where the time goes, `value` says how long it takes.
+    eng_p = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=B, sub_batches=1)
+    eng_p.solve_device(t_in, args.iters, True, t_out=t_out, stream=stream)
+    eng_p.set_profiling(True)
+    eng_p.solve_device(t_in, args.iters, True, t_out=t_out, stream=stream)
     torch.cuda.synchronize(dev)
-    prof = eng.get_profile()
+    prof = eng_p.get_profile()
     for n, (ms, nl) in prof.items():
         fam_ms[n], fam_launch[n] = ms, nl
-    eng.set_profiling(False)
+    eng_p.close()
     t_ms = torch.tensor([ms_total], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
@@ -335,32 +372,90 @@ def main():
     iters_out = t_out["iters"].cpu().numpy()
     ok_dev = bool(np.all(iters_out == args.iters)) and bool(torch.isfinite(t_out["cost"]).all().item())
 
-    # ---- end to end through the host-pointer C-ABI call: pinned host buffers, H2D + D2H inside ----
+    # ---- end to end through the host-pointer C-ABI call: pinned host buffers, H2D + D2H of every step inside ----
+    # ffmpc_solve_batch_host_async + ffmpc_wait: a stream of solves, each copying its own inputs in and its own results out;
+    # a finished sub-batch's results cross PCIe while the next step's other sub-batches are solved.  Two sets of pinned
+    # output buffers alternate (a call in flight owns its buffers until the wait).
     h_in = {k: torch.from_numpy(getattr(inp, k)).pin_memory() for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
     e2e_want = ("xs", "us", "K", "k", "cost", "iters", "ok")
-    h_out = {n: torch.empty(shapes[n], dtype=torch.int32 if n in ("iters", "ok") else torch.float64).pin_memory() for n in e2e_want}
     s_in = _abi.BatchIn()
     s_in.B = B
     for k, t in h_in.items():
         setattr(s_in, k, t.data_ptr())
-    s_out = _abi.BatchOut()
-    for k, t in h_out.items():
-        setattr(s_out, k, t.data_ptr())
+    h_outs, s_outs = [], []
+    for _ in range(2):
+        h_out = {n: torch.empty(shapes[n], dtype=torch.int32 if n in ("iters", "ok") else torch.float64).pin_memory() for n in e2e_want}
+        s_out = _abi.BatchOut()
+        for k, t in h_out.items():
+            setattr(s_out, k, t.data_ptr())
+        h_outs.append(h_out)
+        s_outs.append(s_out)
     h2d = sum(t.numel() * t.element_size() for t in h_in.values())
-    d2h = sum(t.numel() * t.element_size() for t in h_out.values())
-    for _ in range(max(1, min(args.warmup, 2))):
-        eng.solve_host_ptrs(s_in, s_out, args.iters, True)
+    d2h = sum(t.numel() * t.element_size() for t in h_outs[0].values())
+    for i in range(max(2, min(args.warmup, 3))):
+        eng.solve_host_ptrs_async(s_in, s_outs[i % 2], args.iters, True)
+    eng.wait()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        eng.solve_host_ptrs(s_in, s_out, args.iters, True)
-    torch.cuda.synchronize(dev)
+    for i in range(args.steps):
+        eng.solve_host_ptrs_async(s_in, s_outs[i % 2], args.iters, True)
+    eng.wait()
     e2e_s = time.perf_counter() - t0
-    t_e = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    # the same steps one blocking call at a time (ffmpc_solve_batch_host): what a caller without a pipeline sees
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        eng.solve_host_ptrs(s_in, s_outs[i % 2], args.iters, True)
+    e2e_sync_s = time.perf_counter() - t0
+    t_e = torch.tensor([e2e_s, e2e_sync_s], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-    e2e_s = float(t_e.item())
-    e2e_ok = bool(np.isfinite(h_out["cost"].numpy()).all())
+    e2e_s, e2e_sync_s = float(t_e[0].item()), float(t_e[1].item())
+    e2e_ok = all(bool(np.isfinite(h["cost"].numpy()).all()) and bool((h["iters"].numpy() == args.iters).all()) for h in h_outs)
+    d2h_gbs_rank = d2h * args.steps / e2e_s * 1e-9   # this rank's average device->host rate over the pipelined steps
+
+    # ---- strong scaling: BASELINE.json configs[3] as written, `--batch` instances in total sharded over the GPUs ----
+    # (the weak run above solves `--batch` instances on EVERY GPU).  Each rank solves its contiguous slice of the sweep and
+    # the per-instance results cost / iters / ok / f_pred are gathered from device memory over NCCL inside the timed region
+    # (north_star: "only a final result gather over NVLink"); no collective on the solve path.
+    strong = None
+    if world > 1:
+        from franka_force_feedback_mpc_b200 import sharding
+
+        lo, hi = sharding.shard_bounds(B, world, rank)
+        _, _, ginp, _ = make_problem(args, 0, B)          # the one global sweep (rank-0 seeds), sliced
+        shard = ginp.slice(np.arange(lo, hi))
+        Bs = shard.B
+        eng_s = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=Bs, sub_batches=args.sub_batches)
+        ts_in = {k: torch.from_numpy(getattr(shard, k)).to(dev) for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref")}
+        sh = dict(xs=(Bs, N + 1, nx), us=(Bs, N, 7), K=(Bs, N, 7, nx), k=(Bs, N, 7), cost=(Bs,), stop=(Bs,), f_pred=(Bs, 2, 3), iters=(Bs,), ok=(Bs,))
+        ts_out = {n: torch.empty(sh[n], device=dev, dtype=torch.int32 if n in ("iters", "ok") else torch.float64) for n in want}
+        gathered = None
+
+        def step_strong():
+            eng_s.solve_device(ts_in, args.iters, True, t_out=ts_out, stream=stream)
+            with torch.cuda.stream(stream):
+                return sharding.gather_results({n: ts_out[n] for n in ("cost", "iters", "ok", "f_pred")}, B, world, rank, dist=dist, to_numpy=False)
+
+        for _ in range(max(2, min(args.warmup, 3))):
+            step_strong()
+        barrier()
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+        for _ in range(args.steps):
+            gathered = step_strong()
+        with torch.cuda.stream(stream):
+            ev1.record(stream)
+        barrier()
+        t_s = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t_s, op=dist.ReduceOp.MAX)
+        ms_strong = float(t_s.item())
+        strong = {"total": B, "per_gpu": int(sharding.shard_sizes(B, world).max()), "value": B * args.steps / (ms_strong * 1e-3),
+                  "unit": UNIT, "ms_per_step": ms_strong / args.steps, "sub_batches": eng_s.info()["sub_batches"],
+                  "gather": "cost / iters / ok / f_pred all-gathered from device memory (NCCL) inside the timed region"}
+        if rank == 0:
+            strong["gather_ok"] = bool(gathered["cost"].shape[0] == B and torch.isfinite(gathered["cost"]).all().item()
+                                       and (gathered["iters"] == args.iters).all().item())
+        eng_s.close()
 
     if rank != 0:
         if world > 1:
@@ -393,6 +488,16 @@ def main():
                 orc.solve_batch(cfg, model, one, args.iters, True, nthreads=1, _use=lib)
                 cl.append(time.perf_counter() - t0)
             latency["cpu_port_1core_p50_ms"] = float(np.percentile(np.array(cl[2:]) * 1e3, 50))
+        # BASELINE configs 1 and 2: one controller, a stream of warm-started receding-horizon ticks (the reference's loop
+        # runs one such tick per 5 ms, run_classical.py:203-207); kinematic replay of the flat scenario, see tools/tick_stream.py
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import tick_stream
+
+        latency["tick_stream"] = {}
+        for name, variant in (("config1_classical", "classical"), ("config2_ff", "ff")):
+            r, _ = tick_stream.gpu_stream(variant, args.tick_stream_ticks, device=local_rank)
+            latency["tick_stream"][name] = {"p50_ms": r["gpu_tick_ms"]["p50"], "p99_ms": r["gpu_tick_ms"]["p99"], "ticks": r["ticks"],
+                                            "iters_mean": r["iters_mean"], "budget_ms": 5.0, "what": r["gpu_what"], "config": r["config"]}
 
     # ---- rank 0 only: CPU baseline (also counts the rollouts the line search really runs), roofline, latency ----
     cpu = None
@@ -423,17 +528,30 @@ def main():
     except (OSError, ValueError):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = frac_exec = None
+    counters_note = "profiles/kernel_counters.json not found"
+    try:
+        with open(os.path.join(ROOT, "profiles", "kernel_counters.json")) as f:
+            kc = json.load(f)
+        kd = kc["kernels"][dom]
+        units_per_launch = {"node_diff": knots, "backward": B * N, "forward": knots}[dom]   # one launch = the whole (sub-)batch family
+        traffic = kd["dram_bytes_per_unit"] * units_per_launch * args.iters / dom_launches * (rollouts if dom == "forward" else 1.0)
+        flop_exec = kd["flop_executed_per_unit"] * units_per_launch * args.iters * (rollouts if dom == "forward" else 1.0)
+        frac_exec = flop_exec / (fam_ms[dom] * 1e-3) * 1e-12 / peak_tf if (fam_ms[dom] > 0 and peak_tf) else None
+        counters_note = f"profiles/kernel_counters.json (rev {kc['rev']}, {kc['source']}, B={kc['B_per_launch']} per launch): " \
+                        f"{kd['dram_bytes_per_unit']:.0f} B and {kd['flop_executed_per_unit']:.0f} executed FLOP per knot of `{dom}`"
+    except (OSError, ValueError, KeyError):
+        pass
     solve_ms = sum(fam_ms.values())
     roofline = {
         "bound": "fp64",  # neither "hbm" nor "tensor": the path is bound by the fp64 FMA pipe
         "kernel": dom, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
         "peak_source": "fp64 DFMA micro-benchmark run by this bench (ffmpc_dfma_peak); MEASURED_PEAKS.json has no fp64 entry",
         "flop_per_launch": fam_flop[dom] / dom_launches, "ms_per_launch": fam_ms[dom] / dom_launches,
-        # DRAM bytes of the dominant kernel per launch: per-knot figure from the ncu --set full capture committed under
-        # profiles/ (r1d, B=4096: backward 754 MB read + 283 MB written for 204800 knot steps; node_diff 65 MB + 1062 MB for
-        # 208896 knots), scaled to this launch's knots -- about equal to the algorithmic bytes (record 3328 B + gains 1232 B
-        # + gaps / Vxx fs 336 B per knot): no wasted re-reads
-        "traffic": {"backward": 5063.0 * B * N, "node_diff": 5395.0 * knots}.get(dom),
+        # DRAM bytes and executed fp64 work of the dominant kernel per launch: per-knot figures of the ncu --set full capture
+        # named in `counters` (profiles/kernel_counters.json, written by tools/ncu_summary.py --json from the capture of the
+        # revision it names), scaled to this launch's knots
+        "traffic": traffic, "frac_executed": frac_exec, "counters": counters_note,
         "kernel_ms_per_step": {n: fam_ms[n] for n in _abi.FAMILY_NAMES},
         "kernel_share": {n: (fam_ms[n] / solve_ms if solve_ms else None) for n in _abi.FAMILY_NAMES},
         "whole_solve": {
@@ -447,14 +565,28 @@ def main():
         },
     }
 
+    also = None
+    if world == 1 and not args.no_also and args.variant == "ff" and args.contact_model == "normal_1d":
+        # the other throughput configurations of BASELINE.json, short runs (parity for them: tests/test_gpu_parity.py)
+        also = {"config3": short_run(args, local_rank, "classical", "normal_1d", 4096, 10, 1.0),
+                "config5": short_run(args, local_rank, "ff", "point3d", 16384, 20, 0.75)}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_config(args, B, nx),
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ok": e2e_ok},
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ok": e2e_ok,
+                "call": "ffmpc_solve_batch_host_async x steps + ffmpc_wait (pinned host buffers; every step copies its inputs in and its "
+                        "results out)",
+                "blocking_call_value": world * B * args.steps / e2e_sync_s, "d2h_gbs_rank0": d2h_gbs_rank},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "latency": latency, "all_iters_ran": ok_dev,
     }
+    if also is not None:
+        line["also"] = also
+    if strong is not None:
+        # efficiency against the same GPU solving the WHOLE sweep alone = this run's weak per-GPU rate (value / n_gpus)
+        strong["efficiency_vs_1gpu"] = strong["value"] / value
+        line["strong"] = strong
     print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:

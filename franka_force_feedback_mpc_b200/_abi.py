@@ -215,6 +215,8 @@ EXPORTED_SYMBOLS = [
     "ffmpc_destroy",
     "ffmpc_solve_batch",
     "ffmpc_solve_batch_host",
+    "ffmpc_solve_batch_host_async",
+    "ffmpc_wait",
     "ffmpc_node_eval_host",
     "ffmpc_tick_batch",
     "ffmpc_tick_batch_host",

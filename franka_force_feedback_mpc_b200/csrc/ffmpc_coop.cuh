@@ -139,6 +139,13 @@ FFMPC_DEV sv sel6(bool c, const sv &a, const sv &b) {
   return mksv(mk3(c ? a.l.x : b.l.x, c ? a.l.y : b.l.y, c ? a.l.z : b.l.z), mk3(c ? a.a.x : b.a.x, c ? a.a.y : b.a.y, c ? a.a.z : b.a.z));
 }
 
+// Entry j of a 7-wide row of a record tile (8 doubles, the last one padding), one lane per entry: lane 6 writes the
+// padding zero with its entry, so that the warp's store covers whole 32-byte sectors (no partial-sector write-backs).
+FFMPC_DEV void row_store7(double *row, int j, double v) {
+  if (j == NJ - 1) sts2(row + NJ - 1, v, 0.0);
+  else row[j] = v;
+}
+
 // fills the per-block constant table; every thread of the block calls it, followed by __syncthreads()
 FFMPC_DEV void coop_fill_table(const ffmpc_model &mdl, const ffmpc_config &cfg, double *ct) {
   for (int e = (int)threadIdx.x; e < NJ * CT_STRIDE; e += (int)blockDim.x) {
@@ -824,9 +831,9 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
           fgv += fgt[0] * dlt[0][1] + fgt[1] * dlt[1][1];
           fgu += fgt[0] * dlt[0][2] + fgt[1] * dlt[1][2];
         }
-        rec[rec_lz(0, j)] = sc * (sq + fgq) + (eg3 ? eg3[0] : 0.0);
-        rec[rec_lz(1, j)] = sc * (sv_ + fgv) + (eg3 ? eg3[1] : 0.0);
-        rec[rec_lz(2, j)] = sc * (gu + fgu) + (eg3 ? eg3[2] : 0.0);
+        row_store7(rec + rec_lz(0, 0), j, sc * (sq + fgq) + (eg3 ? eg3[0] : 0.0));
+        row_store7(rec + rec_lz(1, 0), j, sc * (sv_ + fgv) + (eg3 ? eg3[1] : 0.0));
+        row_store7(rec + rec_lz(2, 0), j, sc * (gu + fgu) + (eg3 ? eg3[2] : 0.0));
       }
     }
     // Gauss-Newton Hessian: publish own columns, then every lane forms the entries (row joint i, own columns)
@@ -914,9 +921,9 @@ FFMPC_DEV void coop_dam(const ffmpc_model &mdl, const ffmpc_config &cfg, const d
         const double hqq = sc * (sqq + (diag ? hq : 0.0)) + (diag ? ehq : 0.0);
         const double hvv = sc * (svv + (diag ? hv_ : 0.0)) + (diag ? ehv : 0.0);
         const double huu = sc * (suu + (diag ? hu : 0.0)) + (diag ? ehu : 0.0);
-        rec[rec_lzz(0, i, 1, j)] = sc * sqv;
-        rec[rec_lzz(0, i, 2, j)] = sc * squ;
-        rec[rec_lzz(1, i, 2, j)] = sc * svu;
+        row_store7(rec + rec_lzz(0, i, 1, 0), j, sc * sqv);
+        row_store7(rec + rec_lzz(0, i, 2, 0), j, sc * squ);
+        row_store7(rec + rec_lzz(1, i, 2, 0), j, sc * svu);
         if (i & 1) {
           sts2(rec + rec_lzz(0, j, 0, i - 1), pend_q, hqq);
           sts2(rec + rec_lzz(1, j, 1, i - 1), pend_v, hvv);
@@ -1008,8 +1015,8 @@ FFMPC_DEV void coop_action_node(const ffmpc_model &mdl, const ffmpc_config &cfg,
     if (w_w > 0.0) extra += 0.5 * w_w * w * w;
     if (w_soft > 0.0) extra += w_soft * c;
     if (DIFF && wr && act) {
-      rec[REC_LW + j] = w_w * w + w_soft * g;
-      rec[REC_LWW + j] = w_w + w_soft * h;
+      row_store7(rec + REC_LW, j, w_w * w + w_soft * g);
+      row_store7(rec + REC_LWW, j, w_w + w_soft * h);
     }
   }
   cost_out = oct_sum(act ? (scale * cpart + extra) : 0.0) + scale * cuni;

@@ -73,6 +73,7 @@ struct ffmpc_handle {
   int *o_iters = nullptr, *o_ok = nullptr;
   // receding-horizon tick state (ffmpc_tick_batch)
   TickState tick = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int pending_B = 0;        // batch size of host calls enqueued and not yet waited for (0: none)
   int tick_B = -1;          // batch size of the stored plans
   bool plan_dirty = true;   // a solve since the last tick overwrote the workspace the plans live in
   double *d_taubias = nullptr, *o_taucmd = nullptr, *o_tauraw = nullptr, *o_fnpred = nullptr;
@@ -216,6 +217,14 @@ int launch_export(ffmpc_handle *h, const Workspace &ws, cudaStream_t st, const f
   launches += 1;
   if (int e = mark(h, st, FFMPC_FAM_OTHER, 1)) return e;
   CU(cudaGetLastError());
+  return FFMPC_OK;
+}
+
+// waits for every stream of the handle (host calls in flight included)
+int wait_all(ffmpc_handle *h) {
+  for (Sub &sb : h->subs) CU(cudaStreamSynchronize(sb.stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->pending_B = 0;
   return FFMPC_OK;
 }
 
@@ -414,6 +423,7 @@ int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, 
   if (!h || !out) return fail(FFMPC_ERR_ARG, "null handle / out");
   CU(cudaSetDevice(h->device));
   if (int e = check_in(h, in, max_iters)) return e;
+  if (h->pending_B) { if (int e = wait_all(h)) return e; }
   cudaStream_t base = stream ? (cudaStream_t)stream : h->stream;
   const std::vector<Chunk> chunks = plan_chunks(h, (size_t)in->B);
   const bool fan = chunks.size() > 1 && !h->profiling;
@@ -440,10 +450,11 @@ int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, 
   return FFMPC_OK;
 }
 
-int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
-                           const ffmpc_batch_out *out) {
-  if (!h || !out || !in) return fail(FFMPC_ERR_ARG, "null handle / in / out");
-  CU(cudaSetDevice(h->device));
+namespace {
+// Enqueues one host-pointer solve: per sub-batch, on its stream, inputs in -> solve -> export -> results out.  No host
+// synchronisation.  `timed`: bracket the kernels with ev0 / ev1 on the main stream (the synchronous entry point).
+int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters, const ffmpc_batch_out *out, bool timed,
+                 int &launches_out) {
   if (int e = check_in(h, in, max_iters)) return e;
   const size_t Bm = (size_t)h->max_batch, B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx;
   int rc = FFMPC_OK;
@@ -482,13 +493,13 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
   // Each sub-batch is a pipeline of its own on its own stream: inputs in, solve, export, results out.  A finished
   // sub-batch's device->host copies (K alone is 73 KB per instance) overlap the solves of the others; pass pinned host
   // buffers to get asynchronous copies.
-  CU(cudaEventRecord(h->ev0, h->stream));
+  if (timed) CU(cudaEventRecord(h->ev0, h->stream));
   int launches = 0;
   for (size_t c = 0; c < chunks.size(); ++c) {
     Sub &sb = h->subs[c];
     cudaStream_t st = sub_stream(h, c, chunks.size(), h->stream);
     const size_t off = chunks[c].off, cnt = chunks[c].cnt;
-    if (fan) CU(cudaStreamWaitEvent(st, h->ev0, 0));
+    if (fan && timed) CU(cudaStreamWaitEvent(st, h->ev0, 0));
 #define H2D(dst, src, per, T) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyHostToDevice, st))
     H2D(h->d_mode, in->mode, 1, int);
     H2D(h->d_x0, in->x0, nx, double);
@@ -504,7 +515,7 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
     rc = launch_solve(h, sb.ws, st, max_iters, launches);
     if (rc == FFMPC_OK) rc = launch_export(h, sb.ws, st, &dout, off, launches);
     if (rc != FFMPC_OK) return rc;
-    if (fan) {
+    if (fan && timed) {
       CU(cudaEventRecord(sb.done, st));
       CU(cudaStreamWaitEvent(h->stream, sb.done, 0));
     }
@@ -522,17 +533,49 @@ int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_it
 #undef D2H
   }
   // ev1 on the main stream: behind the last kernel of every sub-batch (single stream: behind its copies as well)
-  CU(cudaEventRecord(h->ev1, h->stream));
-  if (fan)
-    for (size_t c = 0; c < chunks.size(); ++c) CU(cudaStreamSynchronize(h->subs[c].stream));
-  CU(cudaStreamSynchronize(h->stream));
+  if (timed) CU(cudaEventRecord(h->ev1, h->stream));
+  h->plan_dirty = true;
+  h->pending_B = in->B;
+  launches_out = launches;
+  return FFMPC_OK;
+}
+
+}  // namespace
+
+int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
+                           const ffmpc_batch_out *out) {
+  if (!h || !out || !in) return fail(FFMPC_ERR_ARG, "null handle / in / out");
+  CU(cudaSetDevice(h->device));
+  if (h->pending_B) { if (int e = wait_all(h)) return e; }
+  int launches = 0;
+  if (int e = host_enqueue(h, in, max_iters, fixed_iters, out, true, launches)) return e;
+  if (int e = wait_all(h)) return e;
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
-  h->plan_dirty = true;
   h->last_ms = ms;
   h->last_launches = launches;
   h->timing_valid = true;
   return FFMPC_OK;
+}
+
+int ffmpc_solve_batch_host_async(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
+                                 const ffmpc_batch_out *out) {
+  if (!h || !out || !in) return fail(FFMPC_ERR_ARG, "null handle / in / out");
+  CU(cudaSetDevice(h->device));
+  // Calls of one batch size pipeline on the sub-batch streams (same instance -> stream map: every staging range is reused
+  // in stream order).  Another batch size maps instances to other streams: drain first.
+  if (h->pending_B && h->pending_B != in->B) { if (int e = wait_all(h)) return e; }
+  int launches = 0;
+  if (int e = host_enqueue(h, in, max_iters, fixed_iters, out, false, launches)) return e;
+  h->last_launches = launches;
+  h->timing_valid = false;
+  return FFMPC_OK;
+}
+
+int ffmpc_wait(ffmpc_handle *h) {
+  if (!h) return fail(FFMPC_ERR_ARG, "null handle");
+  CU(cudaSetDevice(h->device));
+  return wait_all(h);
 }
 
 int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const int *inst, const int *knot, const double *x,
@@ -544,6 +587,7 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
   if (!in->mode || !in->x0 || !in->p_ref || !in->v_ref || !in->x_reg_ref) return fail(FFMPC_ERR_ARG, "mode, x0, p_ref, v_ref, x_reg_ref are required");
   for (int m = 0; m < M; ++m)
     if (inst[m] < 0 || inst[m] >= in->B || knot[m] < 0 || knot[m] > h->N) return fail(FFMPC_ERR_ARG, "inst / knot out of range");
+  if (h->pending_B) { if (int e = wait_all(h)) return e; }
   const size_t B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx, Ms = (size_t)M;
   cudaStream_t st = h->stream;
   // transient device buffers (test hook, not a hot path); nothing of the solver workspace is touched
@@ -697,6 +741,7 @@ int ffmpc_tick_batch_host(ffmpc_handle *h, const ffmpc_tick_in *in, const ffmpc_
   if (in->B > h->max_batch) return fail(FFMPC_ERR_CAPACITY, "batch larger than the handle's max_batch");
   if (!in->mode || !in->x_now || !in->p_ref || !in->v_ref || !in->x_reg_ref || !in->tau_bias)
     return fail(FFMPC_ERR_ARG, "mode, x_now, p_ref, v_ref, x_reg_ref, tau_bias are required");
+  if (h->pending_B) { if (int e = wait_all(h)) return e; }
   const size_t Bm = (size_t)h->max_batch, B = (size_t)in->B, N = (size_t)h->N, nx = (size_t)h->nx;
   int rc = FFMPC_OK;
 #define DA(ptr, count) if (rc == FFMPC_OK && !(ptr)) rc = dalloc(h, &(ptr), (count))

@@ -34,6 +34,8 @@ def _declare(lib):
     lib.ffmpc_destroy.restype = None
     lib.ffmpc_solve_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     lib.ffmpc_solve_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.ffmpc_solve_batch_host_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.ffmpc_wait.argtypes = [C.c_void_p]
     lib.ffmpc_node_eval_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ffmpc_tick_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     lib.ffmpc_tick_batch_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
@@ -120,6 +122,13 @@ class FFMPCEngine:
     def solve_host_ptrs(self, s_in: _abi.BatchIn, s_out: _abi.BatchOut, max_iters: int, fixed_iters: bool = True):
         """Same with pre-built pointer structs (e.g. pinned torch tensors), no allocation per call."""
         self._check(self.lib.ffmpc_solve_batch_host(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
+
+    def solve_host_ptrs_async(self, s_in: _abi.BatchIn, s_out: _abi.BatchOut, max_iters: int, fixed_iters: bool = True):
+        """``ffmpc_solve_batch_host_async``: returns after enqueueing; buffers must stay valid until ``wait()``."""
+        self._check(self.lib.ffmpc_solve_batch_host_async(self._h, C.byref(s_in), int(max_iters), int(bool(fixed_iters)), C.byref(s_out)))
+
+    def wait(self):
+        self._check(self.lib.ffmpc_wait(self._h))
 
     # ---- device API: torch CUDA tensors as buffers, stream-ordered, no sync ----------------------
     def solve_device(self, t_in: dict, max_iters: int, fixed_iters: bool = True, t_out: Optional[dict] = None, stream=None) -> dict:

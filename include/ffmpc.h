@@ -220,6 +220,15 @@ int ffmpc_solve_batch(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, 
 int ffmpc_solve_batch_host(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
                            const ffmpc_batch_out *out);
 
+/* Asynchronous form: enqueues the copies and the solve on the handle's streams and returns.  The host buffers of `in`
+ * and `out` (pinned memory, else the copies block) must stay valid and untouched until ffmpc_wait returns; every call
+ * in flight needs its own output buffers.  Successive calls with the same batch size pipeline: a finished sub-batch's
+ * results cross PCIe while the next call's other sub-batches are already being solved, so a stream of solves runs at the
+ * device rate with the copies hidden.  Any other entry point on the handle waits for the calls in flight first. */
+int ffmpc_solve_batch_host_async(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int fixed_iters,
+                                 const ffmpc_batch_out *out);
+int ffmpc_wait(ffmpc_handle *h);
+
 /* Action-model evaluation at M = B*(number of knots given) points, HOST pointers.
  * knot[i] in [0, N]; knot == N evaluates the terminal model.  x:[M,nx], u:[M,7]. */
 int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const int *inst,

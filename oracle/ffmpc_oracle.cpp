@@ -67,6 +67,41 @@ inline real racos(real x) { return acosq(x); }
 inline real rabs(real x) { return fabsq(x); }
 inline bool rfinite(real x) { return finiteq(x) != 0; }
 inline real rldexp(real x, int e) { return ldexpq(x, e); }
+#elif defined(FFMPC_ORACLE_COUNT)
+// Counting scalar (libffmpc_oracle_count.so): fp64 arithmetic that counts its own operations -- add / sub / mul / div /
+// sqrt / sin / cos / acos = 1 each, so a multiply-add is 2 (SURVEY.md 8d "superseding figure").  What it counts is THIS
+// restatement: forward-mode duals with 21 tangent lanes for every derivative, dense products in the Riccati sweep.
+struct real {
+  double v;
+  real() : v(0.0) {}
+  real(double x) : v(x) {}  // NOLINT implicit on purpose
+  explicit operator double() const { return v; }
+};
+static thread_local long long g_flops_tl = 0;
+std::atomic<long long> g_flops{0};
+#define CNT_BIN(op)                                                                                   \
+  inline real operator op(const real &a, const real &b) { ++g_flops_tl; return real(a.v op b.v); }     \
+  inline real operator op(const real &a, double b) { ++g_flops_tl; return real(a.v op b); }            \
+  inline real operator op(double a, const real &b) { ++g_flops_tl; return real(a op b.v); }
+CNT_BIN(+) CNT_BIN(-) CNT_BIN(*) CNT_BIN(/)
+#define CNT_CMP(op)                                                                  \
+  inline bool operator op(const real &a, const real &b) { return a.v op b.v; }       \
+  inline bool operator op(const real &a, double b) { return a.v op b; }              \
+  inline bool operator op(double a, const real &b) { return a op b.v; }
+CNT_CMP(<) CNT_CMP(>) CNT_CMP(<=) CNT_CMP(>=) CNT_CMP(==) CNT_CMP(!=)
+inline real operator-(const real &a) { return real(-a.v); }
+inline real &operator+=(real &a, const real &b) { ++g_flops_tl; a.v += b.v; return a; }
+inline real &operator-=(real &a, const real &b) { ++g_flops_tl; a.v -= b.v; return a; }
+inline real &operator*=(real &a, const real &b) { ++g_flops_tl; a.v *= b.v; return a; }
+inline real &operator/=(real &a, const real &b) { ++g_flops_tl; a.v /= b.v; return a; }
+#define RPI 3.14159265358979323846
+inline real rsqrt_(real x) { ++g_flops_tl; return std::sqrt(x.v); }
+inline real rsin(real x) { ++g_flops_tl; return std::sin(x.v); }
+inline real rcos(real x) { ++g_flops_tl; return std::cos(x.v); }
+inline real racos(real x) { ++g_flops_tl; return std::acos(x.v); }
+inline real rabs(real x) { return std::fabs(x.v); }
+inline bool rfinite(real x) { return std::isfinite(x.v); }
+inline real rldexp(real x, int e) { return std::ldexp(x.v, e); }
 #else
 typedef double real;
 #define RPI 3.14159265358979323846
@@ -82,6 +117,12 @@ inline real rmin(real a, real b) { return (b < a) ? b : a; }  // std::min / std:
 inline real rmax(real a, real b) { return (a < b) ? b : a; }
 inline real rinf() { return std::numeric_limits<double>::infinity(); }
 inline real rnan() { return std::numeric_limits<double>::quiet_NaN(); }
+#ifdef FFMPC_ORACLE_COUNT
+inline double to_d(const real &x) { return x.v; }
+#else
+inline double to_d(real x) { return (double)x; }
+#endif
+template <class It> void copy_out(It first, It last, double *dst) { for (; first != last; ++first, ++dst) *dst = to_d(*first); }
 
 struct Dual {
   real v;
@@ -1332,16 +1373,20 @@ int ffmpc_oracle_solve_batch(const ffmpc_config *cfg, const ffmpc_model *mdl, co
     if (in->us_init) std::copy(in->us_init + (size_t)b * N * NJ, in->us_init + (size_t)(b + 1) * N * NJ, us0.begin());
     else for (int t = 0; t < N; ++t) for (int i = 0; i < NJ; ++i) us0[t * NJ + i] = (nx == 21) ? P.x0[14 + i] : P.tau_ref[i];
     const bool ok = S.solve(xs0.data(), us0.data(), max_iters, fixed_iters != 0);
-    if (out->xs) std::copy(S.xs.begin(), S.xs.end(), out->xs + (size_t)b * (N + 1) * nx);
-    if (out->us) std::copy(S.us.begin(), S.us.end(), out->us + (size_t)b * N * NJ);
-    if (out->K) std::copy(S.K.begin(), S.K.end(), out->K + (size_t)b * N * NJ * nx);
-    if (out->k) std::copy(S.k.begin(), S.k.end(), out->k + (size_t)b * N * NJ);
-    if (out->gaps) std::copy(S.fs.begin(), S.fs.end(), out->gaps + (size_t)b * (N + 1) * nx);
-    if (out->cost) out->cost[b] = S.cost;
-    if (out->stop) out->stop[b] = S.stop;
+    if (out->xs) copy_out(S.xs.begin(), S.xs.end(), out->xs + (size_t)b * (N + 1) * nx);
+    if (out->us) copy_out(S.us.begin(), S.us.end(), out->us + (size_t)b * N * NJ);
+    if (out->K) copy_out(S.K.begin(), S.K.end(), out->K + (size_t)b * N * NJ * nx);
+    if (out->k) copy_out(S.k.begin(), S.k.end(), out->k + (size_t)b * N * NJ);
+    if (out->gaps) copy_out(S.fs.begin(), S.fs.end(), out->gaps + (size_t)b * (N + 1) * nx);
+    if (out->cost) out->cost[b] = to_d(S.cost);
+    if (out->stop) out->stop[b] = to_d(S.stop);
     if (out->iters) out->iters[b] = S.iter;
     if (out->ok) out->ok[b] = ok ? 1 : 0;
-    if (out->f_pred) for (int t = 0; t < 2; ++t) for (int i = 0; i < 3; ++i) out->f_pred[(size_t)b * 6 + t * 3 + i] = S.f_pred[t][i];
+    if (out->f_pred) for (int t = 0; t < 2; ++t) for (int i = 0; i < 3; ++i) out->f_pred[(size_t)b * 6 + t * 3 + i] = to_d(S.f_pred[t][i]);
+#ifdef FFMPC_ORACLE_COUNT
+    g_flops.fetch_add(g_flops_tl, std::memory_order_relaxed);
+    g_flops_tl = 0;
+#endif
   };
   if (nthreads == 1) {
     for (int b = 0; b < B; ++b) work(b);
@@ -1369,23 +1414,23 @@ int ffmpc_oracle_node_eval(const ffmpc_config *cfg, const ffmpc_model *mdl, cons
     for (int i = 0; i < nx; ++i) xr[i] = x[(size_t)m * nx + i];
     for (int i = 0; i < NJ; ++i) ur[i] = u[(size_t)m * NJ + i];
     node_eval(P, knot[m], xr, ur, true, d);
-    if (out->xnext) for (int i = 0; i < nx; ++i) out->xnext[(size_t)m * nx + i] = d.xnext[i];
-    if (out->cost) out->cost[m] = d.cost;
-    if (out->force) for (int i = 0; i < 3; ++i) out->force[(size_t)m * 3 + i] = d.lam[i];
+    if (out->xnext) for (int i = 0; i < nx; ++i) out->xnext[(size_t)m * nx + i] = to_d(d.xnext[i]);
+    if (out->cost) out->cost[m] = to_d(d.cost);
+    if (out->force) for (int i = 0; i < 3; ++i) out->force[(size_t)m * 3 + i] = to_d(d.lam[i]);
     for (int i = 0; i < nx; ++i) {
       for (int j = 0; j < nx; ++j) {
-        if (out->Fx) out->Fx[((size_t)m * nx + i) * nx + j] = d.Fx[i][j];
-        if (out->Lxx) out->Lxx[((size_t)m * nx + i) * nx + j] = d.Lxx[i][j];
+        if (out->Fx) out->Fx[((size_t)m * nx + i) * nx + j] = to_d(d.Fx[i][j]);
+        if (out->Lxx) out->Lxx[((size_t)m * nx + i) * nx + j] = to_d(d.Lxx[i][j]);
       }
       for (int j = 0; j < NJ; ++j) {
-        if (out->Fu) out->Fu[((size_t)m * nx + i) * NJ + j] = d.Fu[i][j];
-        if (out->Lxu) out->Lxu[((size_t)m * nx + i) * NJ + j] = d.Lxu[i][j];
+        if (out->Fu) out->Fu[((size_t)m * nx + i) * NJ + j] = to_d(d.Fu[i][j]);
+        if (out->Lxu) out->Lxu[((size_t)m * nx + i) * NJ + j] = to_d(d.Lxu[i][j]);
       }
-      if (out->Lx) out->Lx[(size_t)m * nx + i] = d.Lx[i];
+      if (out->Lx) out->Lx[(size_t)m * nx + i] = to_d(d.Lx[i]);
     }
     for (int i = 0; i < NJ; ++i) {
-      if (out->Lu) out->Lu[(size_t)m * NJ + i] = d.Lu[i];
-      for (int j = 0; j < NJ; ++j) if (out->Luu) out->Luu[((size_t)m * NJ + i) * NJ + j] = d.Luu[i][j];
+      if (out->Lu) out->Lu[(size_t)m * NJ + i] = to_d(d.Lu[i]);
+      for (int j = 0; j < NJ; ++j) if (out->Luu) out->Luu[((size_t)m * NJ + i) * NJ + j] = to_d(d.Luu[i][j]);
     }
   }
   return FFMPC_OK;
@@ -1404,44 +1449,64 @@ int ffmpc_oracle_node_calc(const ffmpc_config *cfg, const ffmpc_model *mdl, cons
     for (int i = 0; i < nx; ++i) xr[i] = x[(size_t)m * nx + i];
     for (int i = 0; i < NJ; ++i) ur[i] = u[(size_t)m * NJ + i];
     node_eval(P, knot[m], xr, ur, false, d);
-    if (xnext) for (int i = 0; i < nx; ++i) xnext[(size_t)m * nx + i] = d.xnext[i];
-    if (cost) cost[m] = d.cost;
-    if (force) for (int i = 0; i < 3; ++i) force[(size_t)m * 3 + i] = d.lam[i];
+    if (xnext) for (int i = 0; i < nx; ++i) xnext[(size_t)m * nx + i] = to_d(d.xnext[i]);
+    if (cost) cost[m] = to_d(d.cost);
+    if (force) for (int i = 0; i < 3; ++i) force[(size_t)m * 3 + i] = to_d(d.lam[i]);
   }
   return FFMPC_OK;
 }
 
 // rigid-body primitives for the identity tests: FK of the EE frame, RNEA, CRBA, forward dynamics
+static void to_real7(const double *a, real *r) { for (int i = 0; i < NJ; ++i) r[i] = a ? real(a[i]) : real(0.0); }
+
 void ffmpc_oracle_fk(const ffmpc_model *mdl, const double *q, double *p_ee, double *R_ee) {
-  Kin<double> k;
-  double zero[NJ] = {0, 0, 0, 0, 0, 0, 0};
-  kinematics<double>(*mdl, q, zero, k);
-  p_ee[0] = k.pf.x; p_ee[1] = k.pf.y; p_ee[2] = k.pf.z;
-  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R_ee[3 * i + j] = k.Rf.m[i][j];
+  Kin<real> k;
+  real qr[NJ], zero[NJ];
+  to_real7(q, qr); to_real7(nullptr, zero);
+  kinematics<real>(*mdl, qr, zero, k);
+  p_ee[0] = to_d(k.pf.x); p_ee[1] = to_d(k.pf.y); p_ee[2] = to_d(k.pf.z);
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R_ee[3 * i + j] = to_d(k.Rf.m[i][j]);
 }
 void ffmpc_oracle_rnea(const ffmpc_model *mdl, const double *q, const double *v, const double *a, double *tau) {
-  Kin<double> k;
-  kinematics<double>(*mdl, q, v, k);
-  rnea<double>(*mdl, k, a, nullptr, tau);
+  Kin<real> k;
+  real qr[NJ], vr[NJ], ar[NJ], tr[NJ];
+  to_real7(q, qr); to_real7(v, vr); to_real7(a, ar);
+  kinematics<real>(*mdl, qr, vr, k);
+  rnea<real>(*mdl, k, ar, nullptr, tr);
+  for (int i = 0; i < NJ; ++i) tau[i] = to_d(tr[i]);
 }
 void ffmpc_oracle_crba(const ffmpc_model *mdl, const double *q, double *M) {
-  Kin<double> k;
-  double zero[NJ] = {0, 0, 0, 0, 0, 0, 0};
-  kinematics<double>(*mdl, q, zero, k);
-  double Mm[NJ][NJ];
-  crba<double>(k, Mm);
-  for (int i = 0; i < NJ; ++i) for (int j = 0; j < NJ; ++j) M[i * NJ + j] = Mm[i][j];
+  Kin<real> k;
+  real qr[NJ], zero[NJ];
+  to_real7(q, qr); to_real7(nullptr, zero);
+  kinematics<real>(*mdl, qr, zero, k);
+  real Mm[NJ][NJ];
+  crba<real>(k, Mm);
+  for (int i = 0; i < NJ; ++i) for (int j = 0; j < NJ; ++j) M[i * NJ + j] = to_d(Mm[i][j]);
 }
 // EE frame Jacobian (LOCAL_WORLD_ALIGNED, 6x7, rows [linear; angular]) and frame velocity
 void ffmpc_oracle_frame_jacobian(const ffmpc_model *mdl, const double *q, double *J6) {
-  Kin<double> k;
-  double zero[NJ] = {0, 0, 0, 0, 0, 0, 0};
-  kinematics<double>(*mdl, q, zero, k);
+  Kin<real> k;
+  real qr[NJ], zero[NJ];
+  to_real7(q, qr); to_real7(nullptr, zero);
+  kinematics<real>(*mdl, qr, zero, k);
   for (int j = 0; j < NJ; ++j) {
-    const V3<double> jl = k.J[j].l + cross(k.J[j].a, k.pf);
-    J6[0 * NJ + j] = jl.x; J6[1 * NJ + j] = jl.y; J6[2 * NJ + j] = jl.z;
-    J6[3 * NJ + j] = k.J[j].a.x; J6[4 * NJ + j] = k.J[j].a.y; J6[5 * NJ + j] = k.J[j].a.z;
+    const V3<real> jl = k.J[j].l + cross(k.J[j].a, k.pf);
+    J6[0 * NJ + j] = to_d(jl.x); J6[1 * NJ + j] = to_d(jl.y); J6[2 * NJ + j] = to_d(jl.z);
+    J6[3 * NJ + j] = to_d(k.J[j].a.x); J6[4 * NJ + j] = to_d(k.J[j].a.y); J6[5 * NJ + j] = to_d(k.J[j].a.z);
   }
+}
+
+// counting build only: scalar operations executed since the last reset, summed over the worker threads (-1: not a counting build)
+long long ffmpc_oracle_flops(int reset) {
+#ifdef FFMPC_ORACLE_COUNT
+  const long long v = g_flops.load();
+  if (reset) g_flops = 0;
+  return v;
+#else
+  (void)reset;
+  return -1;
+#endif
 }
 
 }  // extern "C"

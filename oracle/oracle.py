@@ -32,6 +32,8 @@ def build(force: bool = False) -> str:
     )
     stale = stale or not os.path.exists(_FAST_PATH) or os.path.getmtime(_FAST_PATH) < os.path.getmtime(_LIB_PATH)
     stale = stale or not os.path.exists(_QUAD_PATH) or os.path.getmtime(_QUAD_PATH) < os.path.getmtime(_LIB_PATH)
+    cnt = os.path.join(_HERE, "libffmpc_oracle_count.so")
+    stale = stale or not os.path.exists(cnt) or os.path.getmtime(cnt) < os.path.getmtime(_LIB_PATH)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
     return _LIB_PATH
@@ -59,6 +61,18 @@ def quad_lib():
         _quad = C.CDLL(_QUAD_PATH)
         _quad.ffmpc_oracle_last_error.restype = C.c_char_p
     return _quad
+
+
+def count_flops(cfg, model, inp, max_iters: int, fixed_iters: bool = True, nthreads: int = 1) -> float:
+    """Scalar operations (add / sub / mul / div / sqrt / trig = 1 each) the oracle executes per solve of this batch:
+    the same source on a counting scalar (libffmpc_oracle_count.so).  It counts THIS restatement (forward-mode duals,
+    dense Riccati products), not the engine."""
+    build()
+    L = C.CDLL(os.path.join(_HERE, "libffmpc_oracle_count.so"))
+    L.ffmpc_oracle_flops.restype = C.c_longlong
+    L.ffmpc_oracle_flops(1)
+    solve_batch(cfg, model, inp, max_iters, fixed_iters, nthreads=nthreads, _use=L)
+    return L.ffmpc_oracle_flops(1) / float(inp.B)
 
 
 def _cpu_has(*flags) -> bool:

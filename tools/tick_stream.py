@@ -27,26 +27,20 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--variant", default="classical", choices=["classical", "ff"])
-    ap.add_argument("--ticks", type=int, default=1000)
-    ap.add_argument("--t0", type=float, default=0.0)
-    ap.add_argument("--cpu-ticks", type=int, default=300, help="ticks replayed on the CPU port (0 = skip)")
-    args = ap.parse_args()
-
+def gpu_stream(variant: str, ticks: int, t0_s: float = 0.0, keep_plans: int = 0, device: int = 0):
+    """The GPU arm: `ticks` warm-started ticks of one controller through ffmpc_tick_batch_host (B = 1).
+    Returns (result dict, context for the CPU replay)."""
     from franka_force_feedback_mpc_b200 import config, engine, panda, synthetic
-    from franka_force_feedback_mpc_b200.batch import BatchInputs
 
-    ff = args.variant == "ff"
+    ff = variant == "ff"
     N = 40 if ff else 36
     cfgd = (config.benchmark_ff_config if ff else config.benchmark_classical_config)(horizon=N)
     m = panda.default_model()
     cfg, am = config.to_abi(cfgd, m, panda.Q_NEUTRAL), m.to_abi()
     dt, dt_ocp, nx = 0.005, float(cfgd.dt_ocp), 21 if ff else 14
     traj = synthetic.benchmark_trajectory(m)
-    K = args.ticks
-    tk = args.t0 + dt * np.arange(K + 2)
+    K = ticks
+    tk = t0_s + dt * np.arange(K + 2)
     p_mj, _, surf = traj(tk)
     q = synthetic.batched_ik(m, p_mj @ panda.R_MJ_FROM_PIN, panda.reference_R_des(m), panda.Q_NEUTRAL, iters=60)
     dq = np.gradient(q, dt, axis=0)
@@ -55,7 +49,7 @@ def main():
     x_reg = np.concatenate([panda.Q_NEUTRAL, np.zeros(7)])[None]
     pol = config.tick_policy(cfgd, dt_mpc=dt)
 
-    eng = engine.FFMPCEngine(cfg, am, device=0, max_batch=1)
+    eng = engine.FFMPCEngine(cfg, am, device=device, max_batch=1)
     lat, iters, plans = [], [], []
     prev_mode = None
     for k in range(K):
@@ -63,20 +57,35 @@ def main():
         mode = np.array([int(surf[k])], np.int32)
         t0 = time.perf_counter()
         out = eng.tick_host(mode, x_all[k:k + 1], p_ref, v_ref, x_reg, g[k:k + 1], pol, int(cfgd.max_iters), fixed_iters=False,
-                            reset=(k == 0), want_plan=bool(args.cpu_ticks))
+                            reset=(k == 0), want_plan=bool(keep_plans))
         lat.append(time.perf_counter() - t0)
         iters.append(int(out["iters"][0]))
-        if args.cpu_ticks and k < args.cpu_ticks:
+        if keep_plans and k < keep_plans:
             plans.append((mode.copy(), p_ref, v_ref, out["xs"][0].copy(), out["us"][0].copy(), prev_mode is not None and prev_mode == int(mode[0])))
         prev_mode = int(mode[0])
     eng.close()
-    lat = np.array(lat[20:]) * 1e3
+    lat = np.array(lat[min(20, K // 4):]) * 1e3
 
     res = {"config": f"BASELINE config {'2' if ff else '1'}: {'ForceFeedback' if ff else 'Classical'}CrocoddylMPC benchmark preset, N={N}, "
                      f"max_iters={int(cfgd.max_iters)} with early exit, dt=5 ms, kinematic replay of the flat scenario",
            "ticks": K, "gpu_tick_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "mean": float(lat.mean())},
            "gpu_what": "ffmpc_tick_batch_host, B=1, wall clock per tick (H2D + shift + solve + policy + D2H)",
            "iters_mean": float(np.mean(iters)), "realtime_budget_ms": 5.0}
+    return res, dict(plans=plans, cfg=cfg, am=am, cfgd=cfgd, x_all=x_all, x_reg=x_reg, nx=nx, N=N)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--variant", default="classical", choices=["classical", "ff"])
+    ap.add_argument("--ticks", type=int, default=1000)
+    ap.add_argument("--t0", type=float, default=0.0)
+    ap.add_argument("--cpu-ticks", type=int, default=300, help="ticks replayed on the CPU port (0 = skip)")
+    args = ap.parse_args()
+
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+
+    res, ctx = gpu_stream(args.variant, args.ticks, args.t0, keep_plans=args.cpu_ticks)
+    plans, cfg, am, cfgd, x_all, x_reg, nx, N = (ctx[k] for k in ("plans", "cfg", "am", "cfgd", "x_all", "x_reg", "nx", "N"))
     if args.cpu_ticks:
         from oracle import oracle as orc
 
