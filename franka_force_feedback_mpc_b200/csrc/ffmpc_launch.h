@@ -17,7 +17,7 @@
 
 namespace ffmpc {
 #ifndef FFMPC_BWD_WARPS
-#define FFMPC_BWD_WARPS 4   // warps (= instances) per block of the Riccati kernel
+#define FFMPC_BWD_WARPS 1   // warps (= instances) per block of the Riccati kernel
 #endif
 constexpr int kBwdWarps = FFMPC_BWD_WARPS;
 

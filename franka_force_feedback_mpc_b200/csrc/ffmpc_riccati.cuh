@@ -660,12 +660,13 @@ FFMPC_DEV bool riccati_sweep(const Params &P, int b, double *sm, double preg, bo
   return true;
 }
 
-// Residency: FFMPC_BWD_WARPS warps (= instances) per block, FFMPC_BWD_MINBLOCKS blocks per SM (10.4 KB of shared memory per warp).
+// Residency: FFMPC_BWD_WARPS warps (= instances) per block, FFMPC_BWD_MINBLOCKS blocks per SM (10.4 KB of shared memory per warp;
+// 12 one-warp blocks = 168 registers per thread).
 #ifndef FFMPC_BWD_WARPS
-#define FFMPC_BWD_WARPS 4
+#define FFMPC_BWD_WARPS 1
 #endif
 #ifndef FFMPC_BWD_MINBLOCKS
-#define FFMPC_BWD_MINBLOCKS 3
+#define FFMPC_BWD_MINBLOCKS 12
 #endif
 template <bool FF>
 __global__ void __launch_bounds__(FFMPC_BWD_WARPS * 32, FFMPC_BWD_MINBLOCKS) k_backward(const __grid_constant__ Params P) {
@@ -675,8 +676,10 @@ __global__ void __launch_bounds__(FFMPC_BWD_WARPS * 32, FFMPC_BWD_MINBLOCKS) k_b
   extern __shared__ __align__(16) double smem[];
 #endif
   const Workspace &ws = P.ws;
-  const int warp = (int)(threadIdx.x >> 5), lane = (int)(threadIdx.x & 31);
-  const int b = (int)(blockIdx.x * (blockDim.x >> 5)) + warp;
+  // one warp per block by default: the instance index is then a function of blockIdx alone, the early exits below are
+  // provably warp-uniform and the compiler drops the WARPSYNC / ENDCOLLECTIVE pair it otherwise wraps around every shuffle
+  const int warp = (FFMPC_BWD_WARPS == 1) ? 0 : (int)(threadIdx.x >> 5), lane = (int)(threadIdx.x & 31);
+  const int b = (int)blockIdx.x * FFMPC_BWD_WARPS + warp;
   if (b >= ws.B) return;
   if (ws.done[b]) return;
   double *sm = smem + (size_t)warp * BwdSmem::TOTAL;

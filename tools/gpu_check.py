@@ -25,14 +25,14 @@ def parity(ff, nc, cf, B=32, N=50, iters=10):
           "iters_eq", np.array_equal(out["iters"], ref["iters"]), "gap", np.abs(out["gaps"]).max(), flush=True)
     eng.close()
 
-def speed(ff, B, N=50, iters=10, nc=1, cf=1.0, reps=3):
+def speed(ff, B, N=50, iters=10, nc=1, cf=1.0, reps=3, sub_batches=0):
     kw = dict(horizon=N, contact_model="point3d" if nc == 3 else "normal_1d")
     cfgd = config.benchmark_ff_config(**kw) if ff else config.benchmark_classical_config(**kw)
     c = config.to_abi(cfgd, m, panda.Q_NEUTRAL)
     nx = 21 if ff else 14
     s = synthetic.sample_instances(B, N, ff, seed=5, contact_fraction=cf)
     inp = BatchInputs.from_samples(s, nx, N)
-    eng = engine.FFMPCEngine(c, am, 0, B)
+    eng = engine.FFMPCEngine(c, am, 0, B, sub_batches=sub_batches)
     for r in range(reps):
         t = time.time(); out = eng.solve_host(inp, iters, True, want=("xs", "us", "K", "cost", "iters", "ok")); wall = time.time() - t
         ms, nl = eng.last_timing()
@@ -47,7 +47,7 @@ if __name__ == "__main__":
                 parity(ff, nc, cf)
     if what in ("all", "speed"):
         speed(True, 4096); speed(False, 4096); speed(True, 16384); speed(True, 1, reps=5)
-    if what == "prof":
-        speed(True, 4096, iters=2, reps=1)
+    if what == "prof":   # PROF_B instances in PROF_S sub-batches (default: 4096 in 2, i.e. 2048 per launch)
+        speed(True, int(os.environ.get("PROF_B", 4096)), iters=2, reps=1, sub_batches=int(os.environ.get("PROF_S", 0)))
     if what == "lat":
         speed(True, 1, reps=6)
