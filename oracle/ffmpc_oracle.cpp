@@ -1332,17 +1332,19 @@ void ffmpc_oracle_default_config(ffmpc_config *c, int variant) {
   c->w_tangent_pos = 2.0e2; c->w_tangent_vel = 1.0e2; c->w_plane_z = 0.0; c->w_vz = 0.0;
   c->w_unilateral = 5.0e1; c->friction_margin = 1e-3; c->w_fn = 2.0e1; c->fn_des = 8.0;
   c->contact_gains[0] = 0.0; c->contact_gains[1] = 60.0; c->contact_inv_damping = 1.0e-8;
+  if (variant == FFMPC_VARIANT_FF) {
   c->ff_alpha = std::exp(-2.0 * M_PI * 18.0 * 0.01);
   c->w_w = 8.0e-4; c->w_w_soft_limits = 2.0; c->w_y = 3.0e-3;
   const double yq[7] = {0.2, 0.2, 0.2, 0.2, 0.1, 0.1, 0.1}, yv[7] = {0.08, 0.08, 0.08, 0.08, 0.05, 0.05, 0.05},
                yt[7] = {0.35, 0.35, 0.35, 0.35, 0.2, 0.2, 0.2};
   for (int i = 0; i < 7; ++i) { c->y_reg_weights[i] = yq[i]; c->y_reg_weights[7 + i] = yv[i]; c->y_reg_weights[14 + i] = yt[i]; }
+  }
   c->reg_min = 1e-9; c->reg_max = 1e9; c->reg_incfactor = 10.0; c->reg_decfactor = 10.0;
   c->th_stepdec = 0.5; c->th_stepinc = 0.01; c->th_acceptstep = 0.1; c->th_acceptnegstep = 2.0; c->th_grad = 1e-12;
   c->th_stop = 5e-5;  // Box solvers; plain SolverFDDP uses 1e-9
   c->n_alphas = 10;
   c->boxqp_maxiter = 100; c->boxqp_th_acceptstep = 0.1; c->boxqp_th_grad = 1e-5; c->boxqp_reg = 0.0;
-  c->w_friction_cone = 0.0; c->mu = 1.0;
+  c->w_friction_cone = 0.0; c->mu = 0.6;
 }
 
 const char *ffmpc_oracle_last_error(void) { return g_err.c_str(); }

@@ -92,3 +92,62 @@ def run_config_case(make_engine, orc, case, B: int, N: int, iters: int = 1, node
     got = eng.solve_host(inp, iters, True)
     eng.close()
     check_vs_oracle(got, cfg, am, inp, iters, True, orc, label=name)
+
+
+# ---------------------------------------------------------------------------------------------------
+# consumer of tools/export_crocoddyl_golden.py's file (real Crocoddyl results)
+# ---------------------------------------------------------------------------------------------------
+GOLDEN_KNOT_FIELDS = ("xnext", "cost", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+
+
+def check_against_golden(g, make_engine, tol: float = 1e-8):
+    """`g`: mapping with the exporter's arrays.  (1) the exported Pinocchio model constants are compared field by field with
+    the MJCF-derived `panda.default_model()`; every difference is REPORTED (warning) and the run below uses the exported
+    constants -- the model Crocoddyl solved (example_robot_data's URDF with hand + fingers merged into link 7, SURVEY.md
+    App. C) -- never silently the MJCF ones.  (2) knot quantities at the exporter's cold start, so that a solver mismatch
+    is localised.  (3) the solves.  Returns the list of model fields that differ."""
+    import warnings
+
+    from franka_force_feedback_mpc_b200 import config, panda
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+    from franka_force_feedback_mpc_b200.synthetic import batched_gravity_torque
+
+    keys = list(g.files) if hasattr(g, "files") else list(g.keys())
+    m = panda.default_model()
+    exported = {k[4:]: np.asarray(g[k], float) for k in keys if k.startswith("pin_")}
+    assert exported, "golden file without the pin_* model block: regenerate it with the current exporter"
+    differing = []
+    for k, v in exported.items():
+        mine = np.asarray(getattr(m, k), float)
+        if mine.shape != v.shape or not np.allclose(mine, v, rtol=1e-6, atol=1e-9):
+            differing.append(k)
+            d = np.abs(mine.reshape(-1) - v.reshape(-1)).max() if mine.size == v.size else "shape"
+            warnings.warn(f"Panda model constant `{k}` differs between the MJCF-derived default model and the exported one: max |diff| = {d}")
+        setattr(m, k, np.array(v, float))
+    for tag, ff in (("classical", False), ("ff", True)):
+        if f"{tag}_us" not in keys:
+            continue
+        N = g[f"{tag}_us"].shape[1]
+        iters = int(np.max(g[f"{tag}_iter"]))
+        preset = config.benchmark_ff_config if ff else config.benchmark_classical_config
+        cfg = config.to_abi(preset(horizon=N, max_iters=iters), m, panda.Q_NEUTRAL)
+        nx = 21 if ff else 14
+        inp = BatchInputs(nx, N, g[f"{tag}_mode"], g[f"{tag}_x0"], g[f"{tag}_p_ref"], g[f"{tag}_v_ref"], g[f"{tag}_x_reg_ref"])
+        B = inp.B
+        eng = make_engine(cfg, m.to_abi(), B)
+        inst = np.repeat(np.arange(B), N + 1).astype(np.int32)
+        knot = np.tile(np.arange(N + 1), B).astype(np.int32)
+        x = np.repeat(inp.x0, N + 1, axis=0)                                                 # cold start: xs = x0 at every knot,
+        u0 = inp.x0[:, 14:21] if ff else batched_gravity_torque(m, inp.x0[:, :7])            # us = tau_hat (FF) / g(q0) (classical)
+        got = eng.node_eval(inp, inst, knot, x, np.repeat(u0, N + 1, axis=0))
+        for f in GOLDEN_KNOT_FIELDS:
+            want = np.asarray(g[f"{tag}_knot_{f}"], float).reshape(got[f].shape)
+            run = knot < N if f in ("Fu", "Lu", "Lxu", "Luu") else np.ones_like(knot, bool)  # the terminal model has no control blocks
+            assert rel_err(got[f][run], want[run]) < tol, (tag, "knot", f, rel_err(got[f][run], want[run]))
+        out = eng.solve_host(inp, iters, True)
+        eng.close()
+        for k in ("xs", "us", "K", "k", "cost"):
+            a, b = out[k].reshape(B, -1), np.asarray(g[f"{tag}_{k}"], float).reshape(B, -1)
+            e = np.abs(a - b).max(axis=1) / np.maximum(np.abs(b).max(axis=1), 1e-300)
+            assert np.quantile(e, 0.5) < tol, (tag, k, float(np.quantile(e, 0.5)))
+    return differing

@@ -159,3 +159,43 @@ def test_emulated_configuration_matches_oracle(emu, orc, case):
     name, ff, nc, cf, horizon, kw = case
     small = (name, ff, nc, cf, 6 if horizon else None, kw)   # the horizon cases only differ by N: keep them cheap here
     run_config_case(lambda cfg, am, B: _engine(emu, cfg, am, B), orc, small, B=3, N=6, iters=2)
+
+
+def test_golden_consumer_on_an_oracle_made_file(emu, orc):
+    """tests/test_gpu_parity.py::test_against_crocoddyl_golden consumes what tools/export_crocoddyl_golden.py writes on a
+    machine that has Crocoddyl; that file does not exist on this box.  Here the consumer itself is exercised: a file of the
+    SAME format made by the oracle (knot quantities at the cold start, solves), with a model block that differs from the
+    default model in the link-7 inertia, so that the report-and-adopt path of the model comparison runs too."""
+    import warnings
+
+    from ffmpc_cases import GOLDEN_KNOT_FIELDS, check_against_golden
+    from franka_force_feedback_mpc_b200 import config, panda
+    from franka_force_feedback_mpc_b200.batch import BatchInputs
+    from franka_force_feedback_mpc_b200.synthetic import batched_gravity_torque, sample_instances
+
+    B, N, iters = 3, 5, 2
+    m = panda.default_model()
+    m.mass = m.mass.copy(); m.mass[6] += 0.73           # "hand merged into link 7"
+    g = {f"pin_{k}": np.asarray(getattr(m, k), float) for k in ("joint_pos", "joint_rot", "mass", "com", "inertia", "ee_pos", "ee_rot", "q_lower", "q_upper", "gravity")}
+    for tag, ff in (("classical", False), ("ff", True)):
+        preset = config.benchmark_ff_config if ff else config.benchmark_classical_config
+        cfg = config.to_abi(preset(horizon=N, max_iters=iters), m, panda.Q_NEUTRAL)
+        s = sample_instances(B, N, ff, seed=5, contact_fraction=0.75)
+        nx = 21 if ff else 14
+        inp = BatchInputs.from_samples(s, nx, N)
+        inst = np.repeat(np.arange(B), N + 1).astype(np.int32)
+        knot = np.tile(np.arange(N + 1), B).astype(np.int32)
+        u0 = inp.x0[:, 14:21] if ff else batched_gravity_torque(m, inp.x0[:, :7])
+        kn = orc.node_eval(cfg, m.to_abi(), inp, inst, knot, np.repeat(inp.x0, N + 1, axis=0), np.repeat(u0, N + 1, axis=0))
+        for f in GOLDEN_KNOT_FIELDS:
+            g[f"{tag}_knot_{f}"] = kn[f].reshape((B, N + 1) + kn[f].shape[1:])
+        sol = orc.solve_batch(cfg, m.to_abi(), inp, iters, True)
+        for k in ("xs", "us", "K", "k", "cost"):
+            g[f"{tag}_{k}"] = sol[k]
+        g[f"{tag}_iter"] = sol["iters"]
+        for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref"):
+            g[f"{tag}_{k}"] = s[k]
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        differing = check_against_golden(g, lambda cfg, am, B: _engine(emu, cfg, am, B), tol=1e-7)
+    assert differing == ["mass"] and any("mass" in str(x.message) for x in w)

@@ -224,28 +224,16 @@ def test_full_size_properties(built, orc, ff, nc, B, iters, cf):
 def test_against_crocoddyl_golden(built):
     """Parity with REAL Crocoddyl, when someone with the reference's conda environment has produced
     tests/golden/crocoddyl_golden.npz with tools/export_crocoddyl_golden.py.  Neither crocoddyl nor pinocchio can be
-    installed in this image or on the GPU box, so here this reports: Crocoddyl golden unavailable on this box."""
+    installed in this image or on the GPU box, so here this reports: Crocoddyl golden unavailable on this box.
+    (The consumer itself is exercised on the CPU with an oracle-made file of the same format: tests/test_emulator.py.)"""
     import os
+
+    from ffmpc_cases import check_against_golden
 
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "crocoddyl_golden.npz")
     if not os.path.exists(path):
         pytest.skip("Crocoddyl golden: unavailable on this box (needs the reference's conda env; see tools/export_crocoddyl_golden.py)")
-    from franka_force_feedback_mpc_b200 import config, panda
-    from franka_force_feedback_mpc_b200.batch import BatchInputs
-
-    g = np.load(path, allow_pickle=True)
-    m = panda.default_model()
-    for tag, ff in (("classical", False), ("ff", True)):
-        N = g[f"{tag}_us"].shape[1]
-        iters = int(g[f"{tag}_iter"].max())
-        preset = config.benchmark_ff_config if ff else config.benchmark_classical_config
-        cfg = config.to_abi(preset(horizon=N, max_iters=iters), m, panda.Q_NEUTRAL)
-        inp = BatchInputs(21 if ff else 14, N, g[f"{tag}_mode"], g[f"{tag}_x0"], g[f"{tag}_p_ref"], g[f"{tag}_v_ref"], g[f"{tag}_x_reg_ref"])
-        eng = _eng(cfg, m.to_abi(), inp.B)
-        out = eng.solve_host(inp, iters, True)
-        eng.close()
-        for k in ("xs", "us", "K", "k", "cost"):
-            assert np.quantile(_inst_rel(out[k], g[f"{tag}_{k}"]), 0.5) < 1e-8, (tag, k)
+    check_against_golden(np.load(path, allow_pickle=False), _eng)
 
 
 @pytest.mark.parametrize("ff", [False, True])

@@ -9,6 +9,9 @@ so this script has never been executed there ("Crocoddyl golden: unavailable on 
 What it writes, for the seeded synthetic instances of `synthetic.sample_instances` (same seeds as the tests):
   * the reduced Panda model constants as Pinocchio sees them (joint placements, inertias, frame `panda_link8`),
     to be compared with `panda.default_model()` (the MuJoCo-XML-derived constants the engine uses);
+  * per instance and knot, BEFORE any solve: `problem.calc` + `problem.calcDiff` at the cold start (xs_init, us_init):
+    xnext, cost, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu -- a mismatch in a solve can then be localised to a knot
+    quantity (the consumer checks the knots first);
   * per instance: xs, us, K, k, cost, iter after `--iters` iterations of the reference's own
     `_build_problem` + `SolverBoxFDDP.solve(xs_init, us_init, iters, False)` with the convergence test disabled
     (th_stop = 0), classical and force-feedback, contact and free mode.
@@ -61,10 +64,35 @@ def model_constants(model, pin):
         out["joint_rot"].append(np.array(M.rotation))
         out["mass"].append(Y.mass)
         out["com"].append(np.array(Y.lever))
-        out["inertia"].append(np.array(Y.inertia))
+        I = np.array(Y.inertia)
+        out["inertia"].append(np.array([I[0, 0], I[1, 1], I[2, 2], I[0, 1], I[0, 2], I[1, 2]]))   # PandaModel order: xx yy zz xy xz yz
     f = model.frames[model.getFrameId("panda_link8")]
     out["ee_pos"], out["ee_rot"] = np.array(f.placement.translation), np.array(f.placement.rotation)
-    return {k: np.array(v) for k, v in out.items()}
+    out["q_lower"], out["q_upper"] = np.array(model.lowerPositionLimit), np.array(model.upperPositionLimit)
+    out["gravity"] = np.array(model.gravity.linear)
+    return {k: np.array(v, dtype=float) for k, v in out.items()}
+
+
+KNOT_FIELDS = ("xnext", "cost", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+
+
+def knot_quantities(problem, xs0, us0):
+    """ActionData of every knot after problem.calc + calcDiff at (xs0, us0); the terminal knot has no control blocks."""
+    problem.calc(xs0, us0)
+    problem.calcDiff(xs0, us0)
+    datas = list(problem.runningDatas) + [problem.terminalData]
+    nx, nu = len(xs0[0]), len(us0[0])
+    res = {}
+    for f in KNOT_FIELDS:
+        rows = []
+        for t, d in enumerate(datas):
+            v = np.array(getattr(d, f), dtype=float)
+            if t == len(datas) - 1 and f in ("Fu", "Lu", "Lxu", "Luu"):   # terminal model: nu-dependent blocks may be empty
+                shape = {"Fu": (nx, nu), "Lu": (nu,), "Lxu": (nx, nu), "Luu": (nu, nu)}[f]
+                v = np.zeros(shape) if v.size != int(np.prod(shape)) else v.reshape(shape)
+            rows.append(v)
+        res[f] = np.array(rows)
+    return res
 
 
 def main():
@@ -89,9 +117,11 @@ def main():
         ref_cfg = ref_cfg_cls(**{k: v for k, v in vars(ours).items() if k in ref_cfg_cls.__dataclass_fields__})
         ctl, pin = bare_controller(mod, cls_name, ref_cfg, panda.Q_NEUTRAL, R_des)
         if not ff:
-            out["pin_model"] = np.array([model_constants(ctl.model, pin)], dtype=object)
+            for k, v in model_constants(ctl.model, pin).items():
+                out[f"pin_{k}"] = v
         s = synthetic.sample_instances(args.batch, args.horizon, ff, seed=5, contact_fraction=0.75)
         res = {k: [] for k in ("xs", "us", "K", "k", "cost", "iter")}
+        knots = {f: [] for f in KNOT_FIELDS}
         for b in range(args.batch):
             refs = [(s["p_ref"][b, k], s["v_ref"][b, k], bool(s["mode"][b])) for k in range(args.horizon + 1)]
             ctl.traj_fn = lambda t, refs=refs: refs[min(int(round(t / 0.01)), args.horizon)]
@@ -102,12 +132,16 @@ def main():
             ctl.xs = ctl.us = None
             ctl._tau_prev = np.asarray(pin.rnea(ctl.model, ctl.data, x0[:7], np.zeros(7), np.zeros(7)))
             xs0, us0 = ctl._shift_guess(x0, args.horizon)
+            for f, v in knot_quantities(problem, xs0, us0).items():
+                knots[f].append(v)
             solver.solve(xs0, us0, args.iters, False)
             res["xs"].append(np.array(solver.xs)); res["us"].append(np.array(solver.us))
             res["K"].append(np.array(solver.K)); res["k"].append(np.array(solver.k))
             res["cost"].append(solver.cost); res["iter"].append(solver.iter)
         for k, v in res.items():
             out[f"{tag}_{k}"] = np.array(v)
+        for f, v in knots.items():
+            out[f"{tag}_knot_{f}"] = np.array(v)        # [B, N+1, ...] at the cold start
         for k in ("mode", "x0", "p_ref", "v_ref", "x_reg_ref"):
             out[f"{tag}_{k}"] = s[k]
     np.savez_compressed(args.out, **out)

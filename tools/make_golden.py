@@ -318,6 +318,28 @@ def gen_scen():
     print("scen_golden.npz", len(out), "arrays")
 
 
+def gen_defaults():
+    """Defaults of the reference's two config dataclasses (crocoddyl_classical.py:12-110, crocoddyl_force_feedback.py:12-146),
+    field by field, as JSON: config.py and ffmpc_default_config are tested against them (tests/test_config_defaults.py)."""
+    import dataclasses
+    import json
+
+    from src.mpc.crocoddyl_classical import ClassicalMPCConfig
+    from src.mpc.crocoddyl_force_feedback import ForceFeedbackMPCConfig
+
+    def dump(c):
+        out = {}
+        for f in dataclasses.fields(c):
+            v = getattr(c, f.name)
+            out[f.name] = v.tolist() if isinstance(v, np.ndarray) else v
+        return out
+
+    res = {"ClassicalMPCConfig": dump(ClassicalMPCConfig()), "ForceFeedbackMPCConfig": dump(ForceFeedbackMPCConfig())}
+    with open(os.path.join(GOLD, "config_defaults.json"), "w") as f:
+        json.dump(res, f, indent=1, sort_keys=True)
+    print("config_defaults.json", {k: len(v) for k, v in res.items()})
+
+
 def main():
     if not os.path.isdir(REF):
         raise SystemExit(f"{REF} not found: the golden fixtures can only be regenerated where the reference is mounted")
@@ -329,6 +351,7 @@ def main():
     gen_misc()
     gen_ctrl()
     gen_scen()
+    gen_defaults()
 
 
 if __name__ == "__main__":
