@@ -26,8 +26,12 @@ constexpr size_t kFwdCoopSmemBytes = (size_t)(CT_SIZE + (kFwdCoopBlock / 8) * CS
 // bring one 128-byte line into L1 ahead of use (no register cost); the rollout issues these for knot t+1 while knot t
 // is evaluated: its global operands (K_t, xs_t, fs_t, Vxx fs_t, us_t, k_t, references) do not depend on the rollout state
 FFMPC_DEV void prefetch_l1(const void *p) {
-#if !defined(FFMPC_EMU)
+#if !defined(FFMPC_EMU) && !defined(FFMPC_NO_PREFETCH)
+#ifdef FFMPC_PREFETCH_L2
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
 #else
   (void)p;
 #endif
@@ -247,9 +251,14 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
   for (int t = 0; t <= N; ++t) {
     CoopX xt;
     const double *fst = fs + (size_t)t * nx, *xst = xs + (size_t)t * nx, *vft = Vfs + (size_t)t * nx;
-    xt.q = close ? xh.q : xh.q + fst[jj] * (steplength - 1.0);
-    xt.v = close ? xh.v : xh.v + fst[NJ + jj] * (steplength - 1.0);
-    xt.t = FF ? (close ? xh.t : xh.t + fst[2 * NJ + jj] * (steplength - 1.0)) : 0.0;
+    // gaps enter only while the candidate is infeasible and the step is partial (`close` is octet-uniform): no load otherwise
+    xt = xh;
+    if (!close) {
+      xt.q = xh.q + fst[jj] * (steplength - 1.0);
+      xt.v = xh.v + fst[NJ + jj] * (steplength - 1.0);
+      if (FF) xt.t = xh.t + fst[2 * NJ + jj] * (steplength - 1.0);
+    }
+    if (!FF) xt.t = 0.0;
     const double dxq = xt.q - xst[jj], dxv = xt.v - xst[NJ + jj], dxt = FF ? xt.t - xst[2 * NJ + jj] : 0.0;
     if (wlane) {
       double *xw = xt_all + (size_t)t * nx;
@@ -293,8 +302,8 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
       }
       const size_t ro = (size_t)(t + 1) * nx * 8 + 128 * (j & 1);
       if (j < 2) prefetch_l1((const char *)xs + ro);
-      else if (j < 4) prefetch_l1((const char *)fs + ro);
-      else if (j < 6) prefetch_l1((const char *)Vfs + ro);
+      else if (j < 4) { if (!close) prefetch_l1((const char *)fs + ro); }
+      else if (j < 6) { if (!feasible) prefetch_l1((const char *)Vfs + ro); }
       else if (j == 6) prefetch_l1(us + (t + 1) * NJ);
       else prefetch_l1(kb + (t + 1) * NJ);
       if (j == 0) prefetch_l1(ctx.p_ref + 3);
