@@ -16,6 +16,8 @@ ERR_ARG = 1
 ERR_CUDA = 2
 ERR_NO_DEVICE = 3
 ERR_CAPACITY = 4
+STATIC_MAX_POINTS = 512  # FFMPC_STATIC_MAX_POINTS / FFMPC_STATIC_MAX_BATCH (ffmpc_node_eval_static)
+STATIC_MAX_BATCH = 512
 
 VARIANT_CLASSICAL = 0
 VARIANT_FF = 1
@@ -218,6 +220,7 @@ EXPORTED_SYMBOLS = [
     "ffmpc_solve_batch_host_async",
     "ffmpc_wait",
     "ffmpc_node_eval_host",
+    "ffmpc_node_eval_static",
     "ffmpc_tick_batch",
     "ffmpc_tick_batch_host",
     "ffmpc_last_timing",

@@ -52,6 +52,9 @@ struct Chunk {
 
 }  // namespace
 
+// error text for the entry points that live in other translation units (ffmpc_noalloc.cu)
+int ffmpc::set_error(int code, const char *msg) { return fail(code, msg); }
+
 struct ffmpc_handle {
   int device = 0;
   int max_batch = 0;

@@ -21,6 +21,8 @@ namespace ffmpc {
 #endif
 constexpr int kBwdWarps = FFMPC_BWD_WARPS;
 
+// ffmpc_engine.cu: sets the text ffmpc_last_error() returns (this thread), returns `code`
+int set_error(int code, const char *msg);
 // ffmpc_launch_bwd.cu
 int prepare_backward();
 void launch_backward(const Params &P, cudaStream_t st);

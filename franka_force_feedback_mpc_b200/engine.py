@@ -43,6 +43,9 @@ def _declare(lib):
     lib.ffmpc_sync.argtypes = [C.c_void_p]
     lib.ffmpc_get_info.argtypes = [C.c_void_p, C.c_void_p]
     lib.ffmpc_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    if hasattr(lib, "ffmpc_node_eval_static"):  # absent from the test-only host emulator build
+        lib.ffmpc_node_eval_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]
     if hasattr(lib, "ffmpc_dfma_peak"):  # absent from the test-only host emulator build
         lib.ffmpc_dfma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.ffmpc_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
@@ -73,6 +76,44 @@ def dfma_peak_tflops(device: int = 0) -> float:
     if rc != 0:
         raise FFMPCError(f"ffmpc_dfma_peak failed with code {rc}")
     return tf.value
+
+
+def node_eval_static(cfg, model, inp: BatchInputs, inst, knot, x, u, device: int = 0, stream=None) -> dict:
+    """``ffmpc_node_eval_static``: the knot evaluation without any allocation inside the library (scratch in a static
+    device array; limits ``_abi.STATIC_MAX_POINTS`` / ``STATIC_MAX_BATCH``).  The buffers the CALLER owns are torch device
+    tensors made here; the result comes back as numpy arrays.  Calls that overlap on the GPU race on the shared scratch."""
+    import torch
+
+    lib = load_library()
+    dev = torch.device("cuda", device)
+    nx = 21 if cfg.variant == _abi.VARIANT_FF else 14
+    M = int(np.asarray(inst).size)
+    up = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a, dtype=dt)).to(dev)
+    keep = dict(mode=up(inp.mode, np.int32), x0=up(inp.x0, np.float64), p_ref=up(inp.p_ref, np.float64), v_ref=up(inp.v_ref, np.float64),
+                x_reg_ref=up(inp.x_reg_ref, np.float64))
+    for name in ("tau_ref",):
+        v = getattr(inp, name, None)
+        if v is not None:
+            keep[name] = up(v, np.float64)
+    s_in = _abi.BatchIn()
+    s_in.B = inp.B
+    for name, t in keep.items():
+        setattr(s_in, name, t.data_ptr())
+    d_inst, d_knot = up(inst, np.int32), up(knot, np.int32)
+    d_x, d_u = up(np.asarray(x, dtype=np.float64).reshape(M, nx), np.float64), up(np.asarray(u, dtype=np.float64).reshape(M, 7), np.float64)
+    shapes = dict(xnext=(M, nx), cost=(M,), force=(M, 3), Fx=(M, nx, nx), Fu=(M, nx, 7), Lx=(M, nx), Lu=(M, 7), Lxx=(M, nx, nx),
+                  Lxu=(M, nx, 7), Luu=(M, 7, 7))
+    outs = {k: torch.full(sh, float("nan"), dtype=torch.float64, device=dev) for k, sh in shapes.items()}
+    s_out = _abi.NodeOut()
+    for k, t in outs.items():
+        setattr(s_out, k, t.data_ptr())
+    st = stream if stream is not None else torch.cuda.current_stream(dev)
+    rc = lib.ffmpc_node_eval_static(C.byref(cfg), C.byref(model), int(device), C.byref(s_in), M, d_inst.data_ptr(), d_knot.data_ptr(),
+                                    d_x.data_ptr(), d_u.data_ptr(), C.byref(s_out), C.c_void_p(st.cuda_stream))
+    if rc != 0:
+        raise FFMPCError(f"ffmpc_node_eval_static failed ({rc}): {lib.ffmpc_last_error().decode()}")
+    st.synchronize()
+    return {k: t.cpu().numpy() for k, t in outs.items()}
 
 
 class FFMPCEngine:

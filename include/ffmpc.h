@@ -235,6 +235,25 @@ int ffmpc_node_eval_host(ffmpc_handle *h, const ffmpc_batch_in *in, int M, const
                          const int *knot, const double *x, const double *u,
                          const ffmpc_node_out *out);
 
+/* No-allocation variant of the action-model evaluation.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic and kernels as ffmpc_node_eval_host, but: no handle (config and model
+ * are passed), DEVICE pointers for every input and output (all ten outputs required), stream-ordered on `stream`
+ * (a cudaStream_t, NULL = the default stream), returns after enqueueing, and the scratch the kernels need (the knot
+ * records of the M points, the resolved torque reference) lives in one file-scope `static __device__` array of
+ * (FFMPC_STATIC_MAX_POINTS * 592 + FFMPC_STATIC_MAX_BATCH * 7) doubles = 2.4 MB, held by every GPU that loads the
+ * library until the process exits.  The call makes no cudaMalloc / cudaFree / allocating library call; the first call on
+ * a device looks the array's device address up (cudaGetSymbolAddress) and sets the kernels' shared-memory attribute.
+ * M > FFMPC_STATIC_MAX_POINTS or in->B > FFMPC_STATIC_MAX_BATCH is rejected with FFMPC_ERR_CAPACITY.  inst / knot are
+ * device arrays and are NOT range-checked (inst[m] in [0, B), knot[m] in [0, N] is the caller's duty).
+ * Every call shares the one array (it keeps the last call's contents; the call clears what must read zero): calls that
+ * overlap on the GPU -- two streams without an ordering between them, or two host threads -- race on it. */
+#define FFMPC_STATIC_MAX_POINTS 512
+#define FFMPC_STATIC_MAX_BATCH 512
+int ffmpc_node_eval_static(const ffmpc_config *cfg, const ffmpc_model *model, int device, const ffmpc_batch_in *in, int M,
+                           const int *inst, const int *knot, const double *x, const double *u,
+                           const ffmpc_node_out *out, void *stream);
+
 /* ---- Receding-horizon tick for B controllers at once --------------------------------------
  * One call = what `compute_control(obs, t)` does around the solve, for every instance of the batch, on the device:
  *   mode switch -> drop the plan                      crocoddyl_classical.py:321-329
