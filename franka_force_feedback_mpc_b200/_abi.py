@@ -196,8 +196,8 @@ class TickOut(C.Structure):
     ]
 
 
-LS_AUTO, LS_QUEUE, LS_SPECULATIVE = 0, 1, 2
-LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE}
+LS_AUTO, LS_QUEUE, LS_SPECULATIVE, LS_GROUPED, LS_TAIL = 0, 1, 2, 3, 4
+LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE, "grouped": LS_GROUPED, "tail": LS_TAIL}
 
 
 class Options(C.Structure):
@@ -205,7 +205,8 @@ class Options(C.Structure):
 
 
 class Info(C.Structure):
-    _fields_ = [("sub_batches", C.c_int), ("sub_batch_capacity", C.c_int), ("line_search", C.c_int), ("reserved", C.c_int * 5)]
+    _fields_ = [("sub_batches", C.c_int), ("sub_batch_capacity", C.c_int), ("line_search", C.c_int), ("trial_slots", C.c_int),
+                ("reserved", C.c_int * 4)]
 
 
 # every symbol include/ffmpc.h declares (tests check the product library exports all of them)

@@ -176,47 +176,54 @@ FFMPC_DEV bool accept_step(const ffmpc_config &cfg, bool feasible, double steple
 constexpr int TRIAL_REC = 10;  // per (instance, step length) result of a speculative rollout: ok, cost, dv, lam01[6], pad
 
 // ------------------------------------------------------------------------------------------------
-// k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update, ONE step
-// length per launch.  Pass `ia` rolls out alpha = 2^-ia for the instances still searching: pass 0 takes every live
-// instance of the mode bucket (ws.perm), pass ia > 0 takes the compacted queue written by pass ia - 1 (rejected
-// instances are appended with an atomic counter), so warps stay full of useful octets instead of waiting for the
-// slowest of their four instances (measured: 2.4 rollouts per instance and iteration on average, 48 % need more
-// than one).  Same decisions as the sequential loop of SolverFDDP::solve: a trial depends only on its own alpha.
-// One octet per instance; trial trajectory goes to slot 1 - cur.
+// k_forward_coop: SolverFDDP::forwardPass / tryStep / expectedImprovement + acceptance + reg update.
+// The step lengths 2^-ia are tried in PASSES; pass p rolls out the group of `size` consecutive step lengths that starts
+// at `first` (the schedule: Workspace::gfirst / gsize, chosen on the host).  Pass 0 takes every live instance of the mode
+// bucket (ws.perm), pass p > 0 the compacted queue written by pass p - 1 (instances that rejected every step length so
+// far are appended with an atomic counter), so warps stay full of useful octets instead of waiting for the slowest of
+// their four instances (measured: 2.4 rollouts per instance and iteration on average, 48 % need more than one).
+//   size == 1: the pass decides itself (accept / queue for the next pass / give up), as the loop of SolverFDDP::solve.
+//   size  > 1: SPECULATIVE group: gridDim.y = size, every step length of the group is rolled out at once into its own
+//              trial slot and only recorded (ws.trial); k_forward_finalize then takes, per instance, exactly the decisions
+//              of the sequential loop over the group: trials after the first accepted one "never ran".
+// Same decisions and the same arithmetic for every schedule: a trial depends only on its own step length.
+// One octet per (instance, step length); trial slot e of a group = the e-th trajectory slot that is not `cur`.
 // ------------------------------------------------------------------------------------------------
+FFMPC_DEV int trial_slot(int e, int cur) { return e + (e >= cur ? 1 : 0); }
+
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int ia_arg) {
+__global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int pass, int first, int size) {
   const Workspace &ws = P.ws;
-  const bool spec = ws.spec != 0;
-  const int ia = spec ? (int)blockIdx.y : ia_arg;
+  const bool spec = size > 1;
+  const int ia = first + (int)blockIdx.y;
   const ffmpc_config &cfg = P.cfg;
   constexpr int nx = FF ? 21 : 14;
   constexpr int cls = (NC == 0) ? 0 : 1;
   const int nfree = ws.counts[0];
   const int base = (NC == 0) ? 0 : nfree;
-  const int cnt = (ia == 0 || spec) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[ia * 2 + cls];
+  const int cnt = (pass == 0) ? ((NC == 0) ? nfree : ws.counts[1]) : ws.qcount[pass * 2 + cls];
   if ((int)(blockIdx.x * (blockDim.x >> 3)) >= cnt) return;  // whole block without work (block-uniform)
   double *ct = coop_smem_base();
   double *sm = ct + CT_SIZE + (size_t)(threadIdx.x >> 3) * CS_SIZE;
   coop_fill_table(P.mdl, P.cfg, ct);
   __syncthreads();
   const int N = ws.N;
-  const int g = global_tid();  // (blockIdx.x, threadIdx.x) only: blockIdx.y is the step length in speculative mode
+  const int g = global_tid();  // (blockIdx.x, threadIdx.x) only: blockIdx.y is the step length within the group
   const int o = g >> 3, j = g & 7;
   const int jj = j < NJ ? j : NJ - 1;
   const bool act = j < NJ;
   const int lane = (int)(threadIdx.x & 31);
   const unsigned omask = 0xffu << (lane & ~7);
-  const int *items = (ia == 0 || spec) ? (ws.perm + base) : (ws.queue + ((size_t)((ia & 1) * 2 + cls)) * ws.B);
+  const int *items = (pass == 0) ? (ws.perm + base) : (ws.queue + ((size_t)((pass & 1) * 2 + cls)) * ws.B);
   bool valid = o < cnt;
   const int b = items[valid ? o : 0];
-  if (valid && (ia == 0 || spec) && ws.done[b]) valid = false;
+  if (valid && pass == 0 && ws.done[b]) valid = false;
   if (!__any_sync(kFull, valid)) return;
   const int cur = ws.cur[b];
-  const int trial = spec ? (ia + (ia >= cur ? 1 : 0)) : (1 - cur);
+  const int trial = trial_slot(ia - first, cur);
   const bool feasible = ws.feas[b] != 0;
   double cost = ws.cost[b];
-  if (ia == 0 && !spec && !ws.cost_valid[b]) {
+  if (pass == 0 && !spec && !ws.cost_valid[b]) {
     cost = 0.0;  // cost_ = problem.calcDiff(xs, us): sum of the knot costs in order
     for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
   }
@@ -330,8 +337,8 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
   const double dv_all = oct_sum(dv_part);  // unconditional: every lane of the warp takes part in the shuffles
   if (!valid || j != 0) return;
   const double dv = feasible ? 0.0 : dv_all;
-  if (ws.spec) {
-    // speculative mode: only record the trial; k_forward_finalize replays the sequential decisions
+  if (spec) {
+    // speculative group: only record the trial; k_forward_finalize replays the sequential decisions
     double *tr = ws.trial + ((size_t)b * cfg.n_alphas + ia) * TRIAL_REC;
     tr[0] = failed ? 0.0 : 1.0;
     tr[1] = ct_sum;
@@ -347,47 +354,51 @@ __global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coo
     d2 = dq - 2.0 * dv;
     accepted = accept_step(cfg, feasible, steplength, cost - ct_sum, d1, d2);
   }
-  if (ia == 0) {
+  if (pass == 0) {
     ws.cost_valid[b] = 1;
     ws.cost[b] = cost;
   }
   ws.d1[b] = d1;
   ws.d2[b] = d2;
   if (!accepted && ia + 1 < cfg.n_alphas) {
-    // rejected: queue the instance for the next step length
-    const int pos = atomicAdd(&ws.qcount[(ia + 1) * 2 + cls], 1);
-    ws.queue[((size_t)(((ia + 1) & 1) * 2 + cls)) * ws.B + pos] = b;
+    // rejected: queue the instance for the next pass
+    const int pos = atomicAdd(&ws.qcount[(pass + 1) * 2 + cls], 1);
+    ws.queue[((size_t)(((pass + 1) & 1) * 2 + cls)) * ws.B + pos] = b;
     return;
   }
   finish_line_search(ws, cfg, b, it, accepted, feasible, steplength, ct_sum, trial, d1, d2);
 }
 
-// Speculative line search (small batches: latency matters, the GPU is far from full): ALL step lengths are rolled out at
-// once (k_forward_coop with gridDim.y = n_alphas, one trial slot per step length); this kernel then takes, per instance,
-// exactly the decisions of the sequential loop: trials after the first accepted one "never ran".
-static __global__ void k_forward_finalize(const __grid_constant__ Params P, int it) {
+// Decisions of a speculative group (k_forward_coop with size > 1): per instance of pass `pass`, replay the sequential loop
+// over the recorded trials first .. first + size - 1.  Accepted -> finish; every one rejected -> queue for the next pass,
+// or give up after the last step length.  blockIdx.y = mode bucket.
+static __global__ void k_forward_finalize(const __grid_constant__ Params P, int it, int pass, int first, int size) {
   const Workspace &ws = P.ws;
   const ffmpc_config &cfg = P.cfg;
-  const int b = global_tid();
-  if (b >= ws.B || ws.done[b]) return;
+  const int cls = (int)blockIdx.y;
+  const int cnt = (pass == 0) ? ws.counts[cls] : ws.qcount[pass * 2 + cls];
+  const int i = global_tid();
+  if (i >= cnt) return;
+  const int *items = (pass == 0) ? (ws.perm + (cls ? ws.counts[0] : 0)) : (ws.queue + ((size_t)((pass & 1) * 2 + cls)) * ws.B);
+  const int b = items[i];
+  if (pass == 0 && ws.done[b]) return;
   const int N = ws.N;
   const int cur = ws.cur[b];
   const bool feasible = ws.feas[b] != 0;
-  const bool contact = ws.mode[b] == FFMPC_MODE_CONTACT;
   double cost = ws.cost[b];
-  if (!ws.cost_valid[b]) {
+  if (pass == 0 && !ws.cost_valid[b]) {
     cost = 0.0;
     for (int t = 0; t <= N; ++t) cost += ws.ncost[(size_t)b * (N + 1) + t];
   }
   const double dg = ws.dg[b], dq = ws.dq[b];
   double d1 = ws.d1[b], d2 = ws.d2[b], cost_try = 0.0;
   bool accepted = false;
-  int ia_acc = cfg.n_alphas - 1;
-  for (int ia = 0; ia < cfg.n_alphas && !accepted; ++ia) {
+  int ia_acc = first + size - 1;
+  for (int ia = first; ia < first + size && !accepted; ++ia) {
     const double *tr = ws.trial + ((size_t)b * cfg.n_alphas + ia) * TRIAL_REC;
-    if (contact)
-      for (int i = 0; i < 6; ++i)
-        if (!isnan(tr[3 + i])) ws.f_pred[b * 6 + i] = tr[3 + i];
+    if (cls)
+      for (int c = 0; c < 6; ++c)
+        if (!isnan(tr[3 + c])) ws.f_pred[b * 6 + c] = tr[3 + c];
     if (tr[0] != 0.0) {
       const double steplength = ldexp(1.0, -ia);
       const double dv = feasible ? 0.0 : tr[2];
@@ -400,11 +411,18 @@ static __global__ void k_forward_finalize(const __grid_constant__ Params P, int 
       }
     }
   }
-  ws.cost_valid[b] = 1;
-  ws.cost[b] = cost;
+  if (pass == 0) {
+    ws.cost_valid[b] = 1;
+    ws.cost[b] = cost;
+  }
   ws.d1[b] = d1;
   ws.d2[b] = d2;
-  finish_line_search(ws, cfg, b, it, accepted, feasible, ldexp(1.0, -ia_acc), cost_try, ia_acc + (ia_acc >= cur ? 1 : 0), d1, d2);
+  if (!accepted && first + size < cfg.n_alphas) {
+    const int pos = atomicAdd(&ws.qcount[(pass + 1) * 2 + cls], 1);
+    ws.queue[((size_t)(((pass + 1) & 1) * 2 + cls)) * ws.B + pos] = b;
+    return;
+  }
+  finish_line_search(ws, cfg, b, it, accepted, feasible, ldexp(1.0, -ia_acc), cost_try, trial_slot(ia_acc - first, cur), d1, d2);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -144,9 +144,59 @@ std::vector<Chunk> plan_chunks(const ffmpc_handle *h, size_t B) {
   return c;
 }
 
+// ---- line-search schedule -------------------------------------------------------------------------------------
+// The step lengths 2^-ia, ia = 0 .. n-1, are tried in passes over groups of consecutive step lengths; a group of more
+// than one is rolled out speculatively (all at once, decisions replayed in order: ffmpc_coop_kernels.cuh).  Measured on
+// B200 (FF, N = 50, 10 iterations; profiles/r2q_*, r2s_*): 48 % of the instances accept the first step length, the
+// survivors thin out quickly, and a pass over few instances costs the latency of one serial rollout (~0.3 ms) whatever
+// its size.  So: while the GPU is not full, speculation is free and saves passes; once the batch in flight fills the GPU
+// (more than one wave of octets: ~9500 instances), a speculative rollout that turns out unused displaces useful work,
+// and only the late, nearly empty passes are worth merging.
+//   QUEUE       {1}{1/2}{1/4} ... one step length per pass: the loop of SolverFDDP::solve
+//   SPECULATIVE {1, 1/2, ..., 2^-(n-1)} one pass
+//   GROUPED     {1}{1/2, 1/4}{the rest}
+//   TAIL        {1}{1/2}{1/4}{1/8}{1/16}{the rest}
+//   AUTO        by the size of the whole batch of the call: <= 1024 SPECULATIVE, <= 8192 GROUPED, else TAIL
+// (profiles/r2s_ls_sweep_*.txt: FF 65536 instances QUEUE 183.5k / GROUPED 157.7k / TAIL 185.6k solves/s; 4096: 85.0k / 124.1k /
+// 105.3k, SPECULATIVE 92.2k; 512: 15.0k / 35.5k / 21.9k, SPECULATIVE 60.6k; 1024: SPECULATIVE 64.3k, GROUPED 57.9k)
+// A group never exceeds the trial slots the handle allocated (nslots - 1): larger groups are split.
+int resolve_ls(int mode, int batch) {
+  if (mode != FFMPC_LS_AUTO) return mode;
+  return batch <= 1024 ? FFMPC_LS_SPECULATIVE : (batch <= 8192 ? FFMPC_LS_GROUPED : FFMPC_LS_TAIL);
+}
+
+// largest group any call on a handle of capacity max_batch can use (sizes the trial slots)
+int max_group(int mode, int max_batch, int n) {
+  if (mode == FFMPC_LS_QUEUE) return 1;
+  if (mode == FFMPC_LS_SPECULATIVE || (mode == FFMPC_LS_AUTO && max_batch <= 1024)) return n;
+  if (mode == FFMPC_LS_TAIL) return std::max(1, n - 5);
+  return std::max(1, n - 3);  // GROUPED, or AUTO (a small call on a large handle takes the GROUPED schedule)
+}
+
+void set_schedule(Workspace &ws, int call_batch) {
+  const int n = ws.n_alphas, cap = std::max(1, ws.nslots - 1);
+  const int mode = resolve_ls(ws.ls_mode, call_batch);
+  int bounds[34], nb = 0;  // group starts
+  auto cut = [&](int at) { if (at < n && (nb == 0 || bounds[nb - 1] < at)) bounds[nb++] = at; };
+  cut(0);
+  if (mode == FFMPC_LS_QUEUE) for (int i = 1; i < n; ++i) cut(i);
+  else if (mode == FFMPC_LS_GROUPED) { cut(1); cut(3); }
+  else if (mode == FFMPC_LS_TAIL) for (int i = 1; i <= 5; ++i) cut(i);
+  ws.ngroups = 0;
+  for (int g = 0; g < nb; ++g) {
+    const int end = g + 1 < nb ? bounds[g + 1] : n;
+    for (int f = bounds[g]; f < end; f += cap) {
+      ws.gfirst[ws.ngroups] = (signed char)f;
+      ws.gsize[ws.ngroups] = (signed char)std::min(cap, end - f);
+      ws.ngroups++;
+    }
+  }
+}
+
 void bind_chunk(Workspace &ws, const ffmpc_batch_in *in, const Chunk &ck, int max_iters, int fixed_iters) {
   const size_t o = ck.off, N = (size_t)ws.N, nx = (size_t)ws.nx;
   ws.B = (int)ck.cnt;
+  set_schedule(ws, in->B);
   ws.max_iters = max_iters;
   ws.fixed_iters = fixed_iters;
   ws.mode = in->mode + o;
@@ -248,11 +298,10 @@ int alloc_workspace(ffmpc_handle *h, Workspace &ws, size_t B) {
   std::memset(&ws, 0, sizeof(ws));
   ws.N = h->N;
   ws.nx = h->nx;
-  // line search: accepted + one trial slot (queue mode: one launch per step length over the compacted queue of rejected
-  // instances); small batches roll every step length out at once (speculative mode: one trial slot per step length)
-  ws.nslots = 2;
-  ws.spec = (h->opt.line_search == FFMPC_LS_SPECULATIVE || (h->opt.line_search == FFMPC_LS_AUTO && h->max_batch <= 512)) ? 1 : 0;
-  if (ws.spec) ws.nslots = 1 + cfg->n_alphas;
+  // trajectory slots: the accepted candidate + one trial slot per step length of the largest speculative group
+  ws.ls_mode = h->opt.line_search;
+  ws.n_alphas = cfg->n_alphas;
+  ws.nslots = 1 + max_group(h->opt.line_search, h->max_batch, cfg->n_alphas);
   int rc = FFMPC_OK;
 #define DA(ptr, count) if (rc == FFMPC_OK) rc = dalloc(h, &(ptr), (count))
   DA(ws.tau_ref, B * NJ);
@@ -272,7 +321,7 @@ int alloc_workspace(ffmpc_handle *h, Workspace &ws, size_t B) {
   DA(ws.f_pred, B * 6);
   DA(ws.queue, 4 * B);
   DA(ws.qcount, 64);
-  DA(ws.trial, ws.spec ? B * (size_t)cfg->n_alphas * 10 : 1);
+  DA(ws.trial, B * (size_t)cfg->n_alphas * 10);
 #undef DA
   if (rc != FFMPC_OK) return rc;
   // the padding entries of the knot records are never written again (ffmpc_math.cuh: record layout)
@@ -358,7 +407,7 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
   ffmpc_options o;
   ffmpc_default_options(&o);
   if (opt) o = *opt;
-  if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_SPECULATIVE) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
+  if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_TAIL) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
   if (o.sub_batches < 0 || o.sub_batches > FFMPC_MAX_SUB_BATCHES) return fail(FFMPC_ERR_ARG, "options.sub_batches out of range (0 = auto, 1 .. 16)");
   ffmpc_handle *h = new ffmpc_handle();
   h->opt = o;
@@ -846,7 +895,8 @@ int ffmpc_get_info(ffmpc_handle *h, ffmpc_info *info) {
   std::memset(info, 0, sizeof(*info));
   info->sub_batches = (int)h->subs.size();
   info->sub_batch_capacity = h->cap;
-  info->line_search = h->subs[0].ws.spec ? FFMPC_LS_SPECULATIVE : FFMPC_LS_QUEUE;
+  info->line_search = resolve_ls(h->opt.line_search, h->max_batch);  // what a call of max_batch instances resolves to
+  info->trial_slots = h->subs[0].ws.nslots - 1;
   return FFMPC_OK;
 }
 

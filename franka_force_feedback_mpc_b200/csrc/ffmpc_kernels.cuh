@@ -37,9 +37,12 @@ struct Workspace {
   int *feas, *wasfeas, *recalc, *done, *ok, *iter, *cur, *cost_valid;
   double *f_pred;   // [B,2,3]
   int *queue;       // [2 parity][2 mode buckets][B] instances still in the line search (k_forward_coop)
-  int *qcount;      // [32][2] number of queued instances per step-length pass and mode bucket
-  int spec;         // 1: speculative line search (all step lengths at once, small batches), trial slots 1..n_alphas
+  int *qcount;      // [32][2] number of queued instances per line-search pass and mode bucket
   double *trial;    // [B, n_alphas, 10] results of the speculative rollouts
+  // line-search schedule (ffmpc_engine.cu: set_schedule): pass p tries the step lengths 2^-ia, ia = gfirst[p] .. gfirst[p] + gsize[p] - 1;
+  // groups of more than one are rolled out speculatively (needs gsize <= nslots - 1 trial slots)
+  int ls_mode, n_alphas, ngroups;
+  signed char gfirst[32], gsize[32];
 };
 
 struct Params {

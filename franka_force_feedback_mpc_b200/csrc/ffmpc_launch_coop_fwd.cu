@@ -17,39 +17,32 @@ int prepare_coop_fwd() {
   return bad;
 }
 
-// one launch per step length and mode bucket; passes whose queue is empty retire at once (block-uniform early exit)
+// One pass per group of the line-search schedule (Workspace::gfirst / gsize), two launches (mode buckets) per pass, plus
+// the decision kernel behind a speculative group.  Passes whose queue is empty retire at once (block-uniform early exit).
 int launch_forward_coop(const Params &P, int it, cudaStream_t st) {
-  const int grid = (int)(((size_t)P.ws.B * 8 + kFwdCoopBlock - 1) / kFwdCoopBlock);
+  const Workspace &ws = P.ws;
+  const int gx = (int)(((size_t)ws.B * 8 + kFwdCoopBlock - 1) / kFwdCoopBlock);
   const bool ff = P.cfg.variant == FFMPC_VARIANT_FF;
   const int nc = P.cfg.contact_nc;
-  if (P.ws.spec) {
-    // latency mode: every step length in one launch (gridDim.y), then the sequential decisions
-    const dim3 g2((unsigned)grid, (unsigned)P.cfg.n_alphas);
-    if (ff) {
-      FFMPC_LAUNCH((k_forward_coop<0, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-      else FFMPC_LAUNCH((k_forward_coop<3, true>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-    } else {
-      FFMPC_LAUNCH((k_forward_coop<0, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-      else FFMPC_LAUNCH((k_forward_coop<3, false>), g2, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, 0);
-    }
-    FFMPC_LAUNCH(k_forward_finalize, (P.ws.B + 127) / 128, 128, 0, st, P, it);
-    return 3;
-  }
-  cudaMemsetAsync(P.ws.qcount, 0, 32 * 2 * sizeof(int), st);
+  cudaMemsetAsync(ws.qcount, 0, 32 * 2 * sizeof(int), st);
   int launches = 0;
-  for (int ia = 0; ia < P.cfg.n_alphas; ++ia) {
+  for (int p = 0; p < ws.ngroups; ++p) {
+    const int first = ws.gfirst[p], size = ws.gsize[p];
+    const dim3 grid((unsigned)gx, (unsigned)size);
     if (ff) {
-      FFMPC_LAUNCH((k_forward_coop<0, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
-      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
-      else FFMPC_LAUNCH((k_forward_coop<3, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
+      FFMPC_LAUNCH((k_forward_coop<0, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
+      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
+      else FFMPC_LAUNCH((k_forward_coop<3, true>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
     } else {
-      FFMPC_LAUNCH((k_forward_coop<0, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
-      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
-      else FFMPC_LAUNCH((k_forward_coop<3, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, ia);
+      FFMPC_LAUNCH((k_forward_coop<0, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
+      if (nc == 1) FFMPC_LAUNCH((k_forward_coop<1, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
+      else FFMPC_LAUNCH((k_forward_coop<3, false>), grid, kFwdCoopBlock, kFwdCoopSmemBytes, st, P, it, p, first, size);
     }
     launches += 2;
+    if (size > 1) {
+      FFMPC_LAUNCH(k_forward_finalize, dim3((unsigned)((ws.B + 127) / 128), 2u), 128, 0, st, P, it, p, first, size);
+      launches += 1;
+    }
   }
   return launches;
 }

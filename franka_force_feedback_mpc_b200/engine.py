@@ -117,7 +117,8 @@ def node_eval_static(cfg, model, inp: BatchInputs, inst, knot, x, u, device: int
 
 
 class FFMPCEngine:
-    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec"; ``sub_batches``: into how many
+    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec" | "grouped" | "tail"
+    (the schedule of step-length groups, ``FFMPC_LS_*``); ``sub_batches``: into how many
     concurrently scheduled sub-batches (own workspace + stream) a batch is split (0 = auto).  Both only schedule work:
     results are bit-identical."""
 
@@ -231,7 +232,7 @@ class FFMPCEngine:
     def info(self) -> dict:
         i = _abi.Info()
         self._check(self.lib.ffmpc_get_info(self._h, C.byref(i)))
-        return dict(sub_batches=i.sub_batches, sub_batch_capacity=i.sub_batch_capacity,
+        return dict(sub_batches=i.sub_batches, sub_batch_capacity=i.sub_batch_capacity, trial_slots=i.trial_slots,
                     line_search={v: k for k, v in _abi.LINE_SEARCH_MODES.items()}[i.line_search])
 
     def sync(self):

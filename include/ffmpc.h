@@ -179,10 +179,14 @@ void ffmpc_default_config(ffmpc_config *cfg, int variant);
 
 /* Execution options of a handle (how the work is scheduled on the GPU; never what is computed: every mode gives
  * bit-identical results). */
-#define FFMPC_LS_AUTO 0        /* by max_batch: speculative for <= 512 instances, queued above                       */
-#define FFMPC_LS_QUEUE 1       /* one launch per step length over the compacted queue of instances that rejected the
-                                  previous one (same trial sequence as the loop of SolverFDDP::solve)                  */
-#define FFMPC_LS_SPECULATIVE 2 /* every step length rolled out in one launch, decisions replayed in order (latency)   */
+/* Line search: the step lengths 2^-i are tried in passes over groups of consecutive step lengths; a group of more than
+ * one is rolled out at once and the decisions of the sequential loop of SolverFDDP::solve are replayed over it. */
+#define FFMPC_LS_AUTO 0        /* by the batch size of each call: <= 1024 SPECULATIVE, <= 8192 GROUPED, else TAIL         */
+#define FFMPC_LS_QUEUE 1       /* one step length per pass over the compacted queue of instances that rejected the
+                                  previous one (the trial sequence of SolverFDDP::solve)                               */
+#define FFMPC_LS_SPECULATIVE 2 /* every step length in one pass (latency; small batches)                              */
+#define FFMPC_LS_GROUPED 3     /* {1} {1/2, 1/4} {the rest}: three passes (GPU not full)                              */
+#define FFMPC_LS_TAIL 4        /* {1} {1/2} {1/4} {1/8} {1/16} {the rest}: only the nearly empty late passes merged    */
 #define FFMPC_MAX_SUB_BATCHES 16
 typedef struct ffmpc_options {
   int line_search; /* FFMPC_LS_*                                                                                     */
@@ -196,8 +200,10 @@ typedef struct ffmpc_options {
 void ffmpc_default_options(ffmpc_options *opt);
 
 typedef struct ffmpc_info {  /* what a handle resolved its options to */
-  int sub_batches, sub_batch_capacity, line_search;
-  int reserved[5];
+  int sub_batches, sub_batch_capacity;
+  int line_search;  /* FFMPC_LS_* a call of max_batch instances resolves to */
+  int trial_slots;  /* trial trajectory slots per instance = largest speculative group */
+  int reserved[4];
 } ffmpc_info;
 
 /* One handle per GPU; owns workspace for up to max_batch instances; not thread-safe. */

@@ -57,10 +57,11 @@ def test_emulated_node_kernels_match_oracle(emu, orc, ff, nc, cf):
         assert rel_err(a, b) < 1e-10, k
 
 
-# line search: "queue" = one launch per step length with compaction (large batches), "spec" = every step length rolled
-# out at once + k_forward_finalize (handles with max_batch <= 512); ffmpc_options.line_search
+# line search (ffmpc_options.line_search): the schedule of step-length groups; "queue" = one step length per pass with
+# compaction, "spec" = every step length rolled out at once + k_forward_finalize, "grouped" / "tail" = mixtures
 @pytest.mark.parametrize("ff,nc,cf,box,mode", [(False, 1, 1.0, 1, "queue"), (False, 1, 0.0, 1, "spec"), (True, 1, 0.5, 1, "queue"),
-                                               (True, 1, 0.5, 1, "spec"), (True, 3, 1.0, 1, "spec"), (True, 1, 1.0, 0, "queue")])
+                                               (True, 1, 0.5, 1, "spec"), (True, 3, 1.0, 1, "spec"), (True, 1, 1.0, 0, "queue"),
+                                               (True, 1, 0.5, 1, "grouped"), (False, 3, 0.5, 1, "tail")])
 def test_emulated_solver_matches_oracle(emu, orc, ff, nc, cf, box, mode):
     B, N, iters = 5, 12, 6
     cfg, am, inp = make_case(ff, nc, B, N, 5, cf)
@@ -76,6 +77,24 @@ def test_emulated_solver_matches_oracle(emu, orc, ff, nc, cf, box, mode):
     c = inp.mode == 1
     if c.any():
         assert rel_err(out["f_pred"][c], ref["f_pred"][c]) < 1e-6
+
+
+def test_emulated_line_search_schedules_agree_bitwise(emu):
+    """Every schedule takes the same decisions from the same rollouts: bit-identical results (a hard start, so that late
+    step lengths and rejected iterations occur)."""
+    B, N, iters = 6, 10, 5
+    cfg, am, inp = make_case(True, 1, B, N, 23, 0.5)
+    inp.x0[:, :7] += np.random.default_rng(3).normal(0, 0.4, (B, 7))   # far from the references
+    res = {}
+    for ls in ("queue", "spec", "grouped", "tail", "auto"):
+        eng = _engine(emu, cfg, am, B, line_search=ls)
+        res[ls] = eng.solve_host(inp, iters, True)
+        info = eng.info()
+        assert info["trial_slots"] == {"queue": 1, "spec": 10, "grouped": 7, "tail": 5, "auto": 10}[ls]
+        eng.close()
+    for ls in ("spec", "grouped", "tail", "auto"):
+        for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
+            assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
 
 
 def test_emulated_early_exit_and_warm_start(emu, orc):

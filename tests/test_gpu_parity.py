@@ -85,19 +85,30 @@ def test_ten_fixed_iterations_match_oracle(built, orc, ff, nc, cf):
 
 
 def test_line_search_modes_agree_bitwise(built):
-    """The queued line search (one launch per step length, large batches) and the speculative one (all step lengths at
-    once, handles with max_batch <= 512) take the same decisions from the same rollouts: bit-identical results."""
+    """Every line-search schedule (queue / speculative / grouped / tail, and what auto resolves to) takes the same decisions
+    from the same rollouts: bit-identical results.  Then a batch large enough for auto to pick the tail schedule, with
+    sub-batches, against the plain queue on one stream."""
     B, N, iters = 96, 50, 8
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.8)
+    inp.x0[: B // 2, :7] += np.random.default_rng(5).normal(0, 0.3, (B // 2, 7))   # hard starts: late step lengths occur
     res = {}
-    for mode, ls in (("0", "queue"), ("1", "spec")):
+    for ls in ("queue", "spec", "grouped", "tail", "auto"):
         eng = _eng(cfg, am, B, line_search=ls)
-        res[mode] = eng.solve_host(inp, iters, True)
+        res[ls] = eng.solve_host(inp, iters, True)
         eng.close()
-    for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok"):
-        assert np.array_equal(res["0"][k], res["1"][k]), k
-    c = inp.mode == 1
-    assert np.array_equal(res["0"]["f_pred"][c], res["1"]["f_pred"][c])
+    for ls in ("spec", "grouped", "tail", "auto"):
+        for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
+            assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
+    B = 9000
+    cfg, am, inp = make_case(True, 1, B, 20, 10, 0.7)
+    res = {}
+    for ls, sb in (("queue", 1), ("auto", 0), ("grouped", 3)):
+        eng = _eng(cfg, am, B, line_search=ls, sub_batches=sb)
+        res[ls] = eng.solve_host(inp, 5, True)
+        eng.close()
+    for ls in ("auto", "grouped"):
+        for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
+            assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
 
 
 def test_plain_fddp_and_early_exit(built, orc):
