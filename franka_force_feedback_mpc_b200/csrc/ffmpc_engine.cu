@@ -44,6 +44,11 @@ struct Sub {
   Workspace ws;                  // device pointers of this sub-batch's workspace (capacity `cap` instances)
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;    // recorded after the last kernel of the sub-batch
+  // host API: results leave on a copy stream of their own, so that the sub-batch's stream can start the next call's solve
+  // while they cross PCIe (the export staging range is reused only after `copied`)
+  cudaStream_t copy = nullptr;
+  cudaEvent_t exported = nullptr, copied = nullptr;
+  bool copy_pending = false;
 };
 
 struct Chunk {
@@ -275,7 +280,11 @@ int launch_export(ffmpc_handle *h, const Workspace &ws, cudaStream_t st, const f
 
 // waits for every stream of the handle (host calls in flight included)
 int wait_all(ffmpc_handle *h) {
-  for (Sub &sb : h->subs) CU(cudaStreamSynchronize(sb.stream));
+  for (Sub &sb : h->subs) {
+    CU(cudaStreamSynchronize(sb.stream));
+    CU(cudaStreamSynchronize(sb.copy));
+    sb.copy_pending = false;
+  }
   CU(cudaStreamSynchronize(h->stream));
   h->pending_B = 0;
   return FFMPC_OK;
@@ -438,7 +447,10 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
     Sub &sb = h->subs[c];
     const int prio = std::min(prio_least, prio_greatest + c);  // numerically lower = more urgent: the first sub-batch runs first
     if (cudaStreamCreateWithPriority(&sb.stream, cudaStreamNonBlocking, prio) != cudaSuccess ||
-        cudaEventCreateWithFlags(&sb.done, cudaEventDisableTiming) != cudaSuccess)
+        cudaStreamCreateWithFlags(&sb.copy, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sb.done, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sb.exported, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sb.copied, cudaEventDisableTiming) != cudaSuccess)
       rc = fail(FFMPC_ERR_CUDA, "sub-batch stream / event creation failed");
     if (rc == FFMPC_OK) rc = alloc_workspace(h, sb.ws, (size_t)h->cap);
   }
@@ -462,6 +474,9 @@ void ffmpc_destroy(ffmpc_handle *h) {
   for (cudaEvent_t e : h->pev) cudaEventDestroy(e);
   for (Sub &sb : h->subs) {
     if (sb.done) cudaEventDestroy(sb.done);
+    if (sb.exported) cudaEventDestroy(sb.exported);
+    if (sb.copied) cudaEventDestroy(sb.copied);
+    if (sb.copy) cudaStreamDestroy(sb.copy);
     if (sb.stream) cudaStreamDestroy(sb.stream);
   }
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -568,13 +583,21 @@ int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int f
     if (c == 0) { if (int e = mark(h, st, -1, 0)) return e; }
     bind_chunk(sb.ws, &din, chunks[c], max_iters, fixed_iters);
     rc = launch_solve(h, sb.ws, st, max_iters, launches);
+    // the previous call's results of this staging range must have left before the export overwrites them
+    if (rc == FFMPC_OK && sb.copy_pending) CU(cudaStreamWaitEvent(st, sb.copied, 0));
     if (rc == FFMPC_OK) rc = launch_export(h, sb.ws, st, &dout, off, launches);
     if (rc != FFMPC_OK) return rc;
     if (fan && timed) {
       CU(cudaEventRecord(sb.done, st));
       CU(cudaStreamWaitEvent(h->stream, sb.done, 0));
     }
-#define D2H(dst, src, per, T) if (dst) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyDeviceToHost, st))
+    // results out: on the sub-batch's copy stream when sub-batches overlap, else in line
+    cudaStream_t cs = fan ? sb.copy : st;
+    if (fan) {
+      CU(cudaEventRecord(sb.exported, st));
+      CU(cudaStreamWaitEvent(cs, sb.exported, 0));
+    }
+#define D2H(dst, src, per, T) if (dst) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyDeviceToHost, cs))
     D2H(out->xs, h->o_xs, (N + 1) * nx, double);
     D2H(out->us, h->o_us, N * NJ, double);
     D2H(out->K, h->o_K, N * NJ * nx, double);
@@ -586,6 +609,10 @@ int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int f
     D2H(out->iters, h->o_iters, 1, int);
     D2H(out->ok, h->o_ok, 1, int);
 #undef D2H
+    if (fan) {
+      CU(cudaEventRecord(sb.copied, cs));
+      sb.copy_pending = true;
+    }
   }
   // ev1 on the main stream: behind the last kernel of every sub-batch (single stream: behind its copies as well)
   if (timed) CU(cudaEventRecord(h->ev1, h->stream));
@@ -886,7 +913,10 @@ int ffmpc_sync(ffmpc_handle *h) {
   if (!h) return fail(FFMPC_ERR_ARG, "null handle");
   CU(cudaSetDevice(h->device));
   CU(cudaStreamSynchronize(h->stream));
-  for (Sub &sb : h->subs) CU(cudaStreamSynchronize(sb.stream));
+  for (Sub &sb : h->subs) {
+    CU(cudaStreamSynchronize(sb.stream));
+    CU(cudaStreamSynchronize(sb.copy));
+  }
   return FFMPC_OK;
 }
 
