@@ -196,8 +196,8 @@ class TickOut(C.Structure):
     ]
 
 
-LS_AUTO, LS_QUEUE, LS_SPECULATIVE, LS_GROUPED, LS_TAIL = 0, 1, 2, 3, 4
-LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE, "grouped": LS_GROUPED, "tail": LS_TAIL}
+LS_AUTO, LS_QUEUE, LS_SPECULATIVE, LS_GROUPED, LS_TAIL, LS_FILL = 0, 1, 2, 3, 4, 5
+LINE_SEARCH_MODES = {"auto": LS_AUTO, "queue": LS_QUEUE, "spec": LS_SPECULATIVE, "grouped": LS_GROUPED, "tail": LS_TAIL, "fill": LS_FILL}
 
 
 class Options(C.Structure):

@@ -155,28 +155,37 @@ std::vector<Chunk> plan_chunks(const ffmpc_handle *h, size_t B) {
 // B200 (FF, N = 50, 10 iterations; profiles/r2q_*, r2s_*): 48 % of the instances accept the first step length, the
 // survivors thin out quickly, and a pass over few instances costs the latency of one serial rollout (~0.3 ms) whatever
 // its size.  So: while the GPU is not full, speculation is free and saves passes; once the batch in flight fills the GPU
-// (more than one wave of octets: ~9500 instances), a speculative rollout that turns out unused displaces useful work,
+// (more than one wave of octets: 148 SMs x 12 warps x 4 = 7104 instances), a speculative rollout that turns out unused displaces useful work,
 // and only the late, nearly empty passes are worth merging.
 //   QUEUE       {1}{1/2}{1/4} ... one step length per pass: the loop of SolverFDDP::solve
 //   SPECULATIVE {1, 1/2, ..., 2^-(n-1)} one pass
 //   GROUPED     {1}{1/2, 1/4}{the rest}
 //   TAIL        {1}{1/2}{1/4}{1/8}{1/16}{the rest}
-//   AUTO        by the size of the whole batch of the call: <= 1024 SPECULATIVE, <= 8192 GROUPED, else TAIL
-// (profiles/r2s_ls_sweep_*.txt: FF 65536 instances QUEUE 183.5k / GROUPED 157.7k / TAIL 185.6k solves/s; 4096: 85.0k / 124.1k /
-// 105.3k, SPECULATIVE 92.2k; 512: 15.0k / 35.5k / 21.9k, SPECULATIVE 60.6k; 1024: SPECULATIVE 64.3k, GROUPED 57.9k)
+//   FILL        greedy by the size of the whole batch of the call: a pass takes as many step lengths as keep its octets
+//               (expected survivors x group size) within one wave of the rollout kernel; = SPECULATIVE for <= 710
+//               instances, {1 .. 1/32}{rest} at 1024, {1}{1/2}{1/4,1/8}{1/16 .. 1/128}{rest} at 8192, TAIL-like above
+//   AUTO        = FILL
+// profiles/r2s_ls_sweep_*.txt, r2w_fill_sweep.txt (FF, solves/s): 65536 instances QUEUE 183.5k / GROUPED 157.7k / TAIL 185.6k /
+// FILL 186.2k; 8192: 127.9k / 143.5k / 148.4k / 147-155k; 4096: 85.0k / 124.1k / 105.3k / 128.8k; 2048: 50.3k / 88.5k / 68.1k /
+// 100.5k; 1024: SPECULATIVE 64.3k, FILL 70.7k; 512: SPECULATIVE = FILL 60.6k, QUEUE 15.0k.
 // A group never exceeds the trial slots the handle allocated (nslots - 1): larger groups are split.
 int resolve_ls(int mode, int batch) {
-  if (mode != FFMPC_LS_AUTO) return mode;
-  return batch <= 1024 ? FFMPC_LS_SPECULATIVE : (batch <= 8192 ? FFMPC_LS_GROUPED : FFMPC_LS_TAIL);
+  (void)batch;
+  return mode == FFMPC_LS_AUTO ? FFMPC_LS_FILL : mode;
 }
 
 // largest group any call on a handle of capacity max_batch can use (sizes the trial slots)
 int max_group(int mode, int max_batch, int n) {
   if (mode == FFMPC_LS_QUEUE) return 1;
-  if (mode == FFMPC_LS_SPECULATIVE || (mode == FFMPC_LS_AUTO && max_batch <= 1024)) return n;
+  (void)max_batch;
   if (mode == FFMPC_LS_TAIL) return std::max(1, n - 5);
-  return std::max(1, n - 3);  // GROUPED, or AUTO (a small call on a large handle takes the GROUPED schedule)
+  if (mode == FFMPC_LS_GROUPED) return std::max(1, n - 3);
+  return n;  // SPECULATIVE, FILL, AUTO: a small call on any handle may roll every step length out at once
 }
+
+#ifndef FFMPC_FILL_PCT
+#define FFMPC_FILL_PCT 100  // FILL schedule: octets a pass may hold, in percent of one wave of the rollout kernel
+#endif
 
 void set_schedule(Workspace &ws, int call_batch) {
   const int n = ws.n_alphas, cap = std::max(1, ws.nslots - 1);
@@ -187,6 +196,21 @@ void set_schedule(Workspace &ws, int call_batch) {
   if (mode == FFMPC_LS_QUEUE) for (int i = 1; i < n; ++i) cut(i);
   else if (mode == FFMPC_LS_GROUPED) { cut(1); cut(3); }
   else if (mode == FFMPC_LS_TAIL) for (int i = 1; i <= 5; ++i) cut(i);
+  else if (mode == FFMPC_LS_FILL) {
+    // greedy: a pass takes as many step lengths as keep its octets (expected survivors x group size) within one wave of
+    // the rollout kernel (148 SMs x 12 warps x 4 octets); survivors per step length: the cold-start statistics of the
+    // bench workload (bench line, cpu_baseline.trials_per_step_length), a prior that only shapes the schedule
+    static const double surv[10] = {1.0, 0.505, 0.396, 0.292, 0.173, 0.052, 0.0224, 0.0205, 0.0198, 0.0194};
+    const double wave = 148.0 * 12 * 4 * (FFMPC_FILL_PCT / 100.0);
+    int i = 0;
+    while (i < n) {
+      const double f = surv[std::min(i, 9)] * call_batch;
+      int g = 1;
+      while (i + g < n && f * (g + 1) <= wave) ++g;
+      i += g;
+      cut(i);
+    }
+  }
   ws.ngroups = 0;
   for (int g = 0; g < nb; ++g) {
     const int end = g + 1 < nb ? bounds[g + 1] : n;
@@ -416,7 +440,7 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
   ffmpc_options o;
   ffmpc_default_options(&o);
   if (opt) o = *opt;
-  if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_TAIL) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
+  if (o.line_search < FFMPC_LS_AUTO || o.line_search > FFMPC_LS_FILL) return fail(FFMPC_ERR_ARG, "options.line_search out of range");
   if (o.sub_batches < 0 || o.sub_batches > FFMPC_MAX_SUB_BATCHES) return fail(FFMPC_ERR_ARG, "options.sub_batches out of range (0 = auto, 1 .. 16)");
   ffmpc_handle *h = new ffmpc_handle();
   h->opt = o;
@@ -429,9 +453,10 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
   // sub-batches, auto: measured on B200 (profiles/r2d_*): device throughput is flat in the split at 65536 instances and
   // gains 3-7 % at 8192 / 16384 (kernel tails and late line-search passes overlap), the host API gains 10-16 % (result
   // copies overlap the other sub-batches' solves); below 4096 instances one stream, and the speculative line search of
-  // small handles wants the whole batch in one launch
+  // small handles wants the whole batch in one launch; r2v_subbatch_sweep.txt (FILL / TAIL schedules): 16384 instances 2 sub-batches
+  // 168.9k solves/s, 4: 162.8k, 1: 167.0k
   int S = o.sub_batches;
-  if (S == 0) S = max_batch < 4096 ? 1 : (max_batch < 16384 ? 2 : 4);
+  if (S == 0) S = max_batch < 4096 ? 1 : (max_batch < 32768 ? 2 : 4);
   S = std::max(1, std::min(S, max_batch));
   h->opt.sub_batches = S;
   h->cap = (max_batch + S - 1) / S;

@@ -181,12 +181,14 @@ void ffmpc_default_config(ffmpc_config *cfg, int variant);
  * bit-identical results). */
 /* Line search: the step lengths 2^-i are tried in passes over groups of consecutive step lengths; a group of more than
  * one is rolled out at once and the decisions of the sequential loop of SolverFDDP::solve are replayed over it. */
-#define FFMPC_LS_AUTO 0        /* by the batch size of each call: <= 1024 SPECULATIVE, <= 8192 GROUPED, else TAIL         */
+#define FFMPC_LS_AUTO 0        /* = FFMPC_LS_FILL                                                                      */
 #define FFMPC_LS_QUEUE 1       /* one step length per pass over the compacted queue of instances that rejected the
                                   previous one (the trial sequence of SolverFDDP::solve)                               */
 #define FFMPC_LS_SPECULATIVE 2 /* every step length in one pass (latency; small batches)                              */
 #define FFMPC_LS_GROUPED 3     /* {1} {1/2, 1/4} {the rest}: three passes (GPU not full)                              */
 #define FFMPC_LS_TAIL 4        /* {1} {1/2} {1/4} {1/8} {1/16} {the rest}: only the nearly empty late passes merged    */
+#define FFMPC_LS_FILL 5        /* greedy by the batch size of each call: a pass takes as many step lengths as fit one
+                                  wave of the rollout kernel (small batches: all at once; large: like TAIL)            */
 #define FFMPC_MAX_SUB_BATCHES 16
 typedef struct ffmpc_options {
   int line_search; /* FFMPC_LS_*                                                                                     */
@@ -194,7 +196,7 @@ typedef struct ffmpc_options {
                       CUDA stream, stream priority falling with the index: later sub-batches fill what the earlier
                       ones leave idle (kernel tails, the late line-search passes), and in the host API a finished
                       sub-batch's results cross PCIe while the others are still solved.  0 = auto (1 below 4096
-                      instances of capacity, 2 below 16384, else 4), 1 = none, up to FFMPC_MAX_SUB_BATCHES.         */
+                      instances of capacity, 2 below 32768, else 4), 1 = none, up to FFMPC_MAX_SUB_BATCHES.         */
   int reserved[6];
 } ffmpc_options;
 void ffmpc_default_options(ffmpc_options *opt);

@@ -86,13 +86,13 @@ def test_emulated_line_search_schedules_agree_bitwise(emu):
     cfg, am, inp = make_case(True, 1, B, N, 23, 0.5)
     inp.x0[:, :7] += np.random.default_rng(3).normal(0, 0.4, (B, 7))   # far from the references
     res = {}
-    for ls in ("queue", "spec", "grouped", "tail", "auto"):
+    for ls in ("queue", "spec", "grouped", "tail", "fill", "auto"):
         eng = _engine(emu, cfg, am, B, line_search=ls)
         res[ls] = eng.solve_host(inp, iters, True)
         info = eng.info()
-        assert info["trial_slots"] == {"queue": 1, "spec": 10, "grouped": 7, "tail": 5, "auto": 10}[ls]
+        assert info["trial_slots"] == {"queue": 1, "spec": 10, "grouped": 7, "tail": 5, "fill": 10, "auto": 10}[ls]
         eng.close()
-    for ls in ("spec", "grouped", "tail", "auto"):
+    for ls in ("spec", "grouped", "tail", "fill", "auto"):
         for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
             assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
 

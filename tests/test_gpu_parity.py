@@ -92,21 +92,21 @@ def test_line_search_modes_agree_bitwise(built):
     cfg, am, inp = make_case(True, 1, B, N, 9, 0.8)
     inp.x0[: B // 2, :7] += np.random.default_rng(5).normal(0, 0.3, (B // 2, 7))   # hard starts: late step lengths occur
     res = {}
-    for ls in ("queue", "spec", "grouped", "tail", "auto"):
+    for ls in ("queue", "spec", "grouped", "tail", "fill", "auto"):
         eng = _eng(cfg, am, B, line_search=ls)
         res[ls] = eng.solve_host(inp, iters, True)
         eng.close()
-    for ls in ("spec", "grouped", "tail", "auto"):
+    for ls in ("spec", "grouped", "tail", "fill", "auto"):
         for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
             assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
     B = 9000
     cfg, am, inp = make_case(True, 1, B, 20, 10, 0.7)
     res = {}
-    for ls, sb in (("queue", 1), ("auto", 0), ("grouped", 3)):
+    for ls, sb in (("queue", 1), ("auto", 0), ("grouped", 3), ("fill", 2)):
         eng = _eng(cfg, am, B, line_search=ls, sub_batches=sb)
         res[ls] = eng.solve_host(inp, 5, True)
         eng.close()
-    for ls in ("auto", "grouped"):
+    for ls in ("auto", "grouped", "fill"):
         for k in ("xs", "us", "K", "k", "cost", "stop", "gaps", "iters", "ok", "f_pred"):
             assert np.array_equal(res["queue"][k], res[ls][k], equal_nan=True), (ls, k)
 
