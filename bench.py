@@ -285,6 +285,39 @@ def workload_config(args, B: int, nx: int) -> dict:
     }
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this process (and with it the first-touch placement of its pinned host buffers) to the CPUs of the NUMA node its GPU
+    hangs off, so that eight ranks do not all write their results into one node's memory.  Best effort: returns what it did."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        node = -1
+        for cand in (bus, bus[4:] if len(bus) > 12 else bus):   # nvml prints an 8-digit domain, sysfs a 4-digit one
+            path = f"/sys/bus/pci/devices/{cand}/numa_node"
+            if os.path.exists(path):
+                node = int(open(path).read().strip())
+                break
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        info = {"gpu_numa_node": node, "host_numa_nodes": len(nodes), "bound": False}
+        if node >= 0 and len(nodes) > 1:
+            cpus = set()
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                info["bound"] = True
+                info["cpus"] = len(cpus)
+        return info
+    except Exception as e:  # no nvml / sysfs: run unbound
+        return {"bound": False, "error": type(e).__name__}
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -305,6 +338,7 @@ def main():
 
     if not os.path.exists(ge.LIB):
         ge.build_cuda()
+    numa = bind_to_gpu_numa_node(local_rank)
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -577,7 +611,8 @@ def main():
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ok": e2e_ok,
                 "call": "ffmpc_solve_batch_host_async x steps + ffmpc_wait (pinned host buffers; every step copies its inputs in and its "
                         "results out)",
-                "blocking_call_value": world * B * args.steps / e2e_sync_s, "d2h_gbs_rank0": d2h_gbs_rank},
+                "blocking_call_value": world * B * args.steps / e2e_sync_s, "d2h_gbs_rank0": d2h_gbs_rank,
+                "numa_rank0": numa},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "latency": latency, "all_iters_ran": ok_dev,
     }

@@ -161,9 +161,10 @@ std::vector<Chunk> plan_chunks(const ffmpc_handle *h, size_t B) {
 //   SPECULATIVE {1, 1/2, ..., 2^-(n-1)} one pass
 //   GROUPED     {1}{1/2, 1/4}{the rest}
 //   TAIL        {1}{1/2}{1/4}{1/8}{1/16}{the rest}
-//   FILL        greedy by the size of the whole batch of the call: a pass takes as many step lengths as keep its octets
-//               (expected survivors x group size) within one wave of the rollout kernel; = SPECULATIVE for <= 710
-//               instances, {1 .. 1/32}{rest} at 1024, {1}{1/2}{1/4,1/8}{1/16 .. 1/128}{rest} at 8192, TAIL-like above
+//   FILL        by the size of the whole batch of the call, the partition that minimises a two-term cost model (a lone pass
+//               costs one rollout latency; every speculative rollout costs its share of throughput): SPECULATIVE up to 512
+//               instances, {1 .. 1/8}{rest} at 1024 / 2048, {1}{1/2 .. 1/16}{rest} at 4096, {1}{1/2,1/4}{1/8,1/16}{rest} at 8192,
+//               {1}{1/2}{1/4}{1/8}{1/16}{1/32}{rest} from 16384 on
 //   AUTO        = FILL
 // profiles/r2s_ls_sweep_*.txt, r2w_fill_sweep.txt (FF, solves/s): 65536 instances QUEUE 183.5k / GROUPED 157.7k / TAIL 185.6k /
 // FILL 186.2k; 8192: 127.9k / 143.5k / 148.4k / 147-155k; 4096: 85.0k / 124.1k / 105.3k / 128.8k; 2048: 50.3k / 88.5k / 68.1k /
@@ -183,8 +184,8 @@ int max_group(int mode, int max_batch, int n) {
   return n;  // SPECULATIVE, FILL, AUTO: a small call on any handle may roll every step length out at once
 }
 
-#ifndef FFMPC_FILL_PCT
-#define FFMPC_FILL_PCT 100  // FILL schedule: octets a pass may hold, in percent of one wave of the rollout kernel
+#ifndef FFMPC_LS_LONE_PASS
+#define FFMPC_LS_LONE_PASS 3780  // FILL schedule: a pass on an otherwise idle GPU costs as much as this many rollouts at full throughput
 #endif
 
 void set_schedule(Workspace &ws, int call_batch) {
@@ -197,19 +198,28 @@ void set_schedule(Workspace &ws, int call_batch) {
   else if (mode == FFMPC_LS_GROUPED) { cut(1); cut(3); }
   else if (mode == FFMPC_LS_TAIL) for (int i = 1; i <= 5; ++i) cut(i);
   else if (mode == FFMPC_LS_FILL) {
-    // greedy: a pass takes as many step lengths as keep its octets (expected survivors x group size) within one wave of
-    // the rollout kernel (148 SMs x 12 warps x 4 octets); survivors per step length: the cold-start statistics of the
-    // bench workload (bench line, cpu_baseline.trials_per_step_length), a prior that only shapes the schedule
+    // Cost model of one line search, in units of one rollout at full throughput (measured, FF N = 50: 0.082 us):
+    //   a pass over a group of g step lengths starting at step i costs  R_eff + g * surv[i] * B
+    // surv[i] B = instances that rejected every step length before i (the cold-start statistics of the bench workload,
+    // bench line cpu_baseline.trials_per_step_length: a prior that only shapes the schedule); R = what a lone pass costs
+    // whatever its size, the latency of one serial rollout (0.31 ms = 3780 rollouts of throughput); when the call holds more
+    // instances than one wave of the rollout kernel (148 SMs x 12 warps x 4 octets) other work hides that latency in
+    // proportion.  The partition of the n step lengths into consecutive groups that minimises the sum: dynamic programme.
     static const double surv[10] = {1.0, 0.505, 0.396, 0.292, 0.173, 0.052, 0.0224, 0.0205, 0.0198, 0.0194};
-    const double wave = 148.0 * 12 * 4 * (FFMPC_FILL_PCT / 100.0);
-    int i = 0;
-    while (i < n) {
+    const double wave = 148.0 * 12 * 4;
+    const double Reff = (double)FFMPC_LS_LONE_PASS * std::min(1.0, wave / (double)call_batch);
+    double best[33];
+    int take[33];
+    best[n] = 0.0;
+    for (int i = n - 1; i >= 0; --i) {
+      best[i] = 1e300;
       const double f = surv[std::min(i, 9)] * call_batch;
-      int g = 1;
-      while (i + g < n && f * (g + 1) <= wave) ++g;
-      i += g;
-      cut(i);
+      for (int g = 1; i + g <= n && g <= cap; ++g) {
+        const double c = Reff + g * f + best[i + g];
+        if (c < best[i]) { best[i] = c; take[i] = g; }
+      }
     }
+    for (int i = 0; i < n; i += take[i]) cut(i);
   }
   ws.ngroups = 0;
   for (int g = 0; g < nb; ++g) {

@@ -187,8 +187,8 @@ void ffmpc_default_config(ffmpc_config *cfg, int variant);
 #define FFMPC_LS_SPECULATIVE 2 /* every step length in one pass (latency; small batches)                              */
 #define FFMPC_LS_GROUPED 3     /* {1} {1/2, 1/4} {the rest}: three passes (GPU not full)                              */
 #define FFMPC_LS_TAIL 4        /* {1} {1/2} {1/4} {1/8} {1/16} {the rest}: only the nearly empty late passes merged    */
-#define FFMPC_LS_FILL 5        /* greedy by the batch size of each call: a pass takes as many step lengths as fit one
-                                  wave of the rollout kernel (small batches: all at once; large: like TAIL)            */
+#define FFMPC_LS_FILL 5        /* by the batch size of each call: the grouping that minimises a latency + throughput
+                                  cost model (small batches: all at once; 8192: {1}{1/2,1/4}{1/8,1/16}{rest}; large: ~TAIL) */
 #define FFMPC_MAX_SUB_BATCHES 16
 typedef struct ffmpc_options {
   int line_search; /* FFMPC_LS_*                                                                                     */
