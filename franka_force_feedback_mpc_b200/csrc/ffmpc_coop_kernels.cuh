@@ -10,7 +10,10 @@
 
 namespace ffmpc {
 
-constexpr int kCoopBlock = 128;
+#ifndef FFMPC_COOP_BLOCK
+#define FFMPC_COOP_BLOCK 128   // threads per block of the knot-evaluation kernels (16 knots)
+#endif
+constexpr int kCoopBlock = FFMPC_COOP_BLOCK;
 #ifndef FFMPC_COOP_MINBLOCKS
 #define FFMPC_COOP_MINBLOCKS 3  // resident blocks per SM the register allocation is sized for
 #endif
@@ -192,7 +195,7 @@ constexpr int TRIAL_REC = 10;  // per (instance, step length) result of a specul
 FFMPC_DEV int trial_slot(int e, int cur) { return e + (e >= cur ? 1 : 0); }
 
 template <int NC, bool FF>
-__global__ void __launch_bounds__(kCoopBlock, FFMPC_FWD_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int pass, int first, int size) {
+__global__ void __launch_bounds__(128, FFMPC_FWD_MINBLOCKS) k_forward_coop(const __grid_constant__ Params P, int it, int pass, int first, int size) {
   const Workspace &ws = P.ws;
   const bool spec = size > 1;
   const int ia = first + (int)blockIdx.y;
