@@ -60,7 +60,9 @@ def gather_results(local: Dict[str, object], total: int, world: int, rank: int, 
 
     sizes = shard_sizes(total, world)
     cap = int(sizes.max())
-    out = {} if rank == 0 else None
+    # ONE collective: every array's rows are packed side by side into one byte matrix [cap, row_bytes] (the per-instance
+    # results are tens of bytes; four separate all-gathers cost four collective latencies for half a megabyte)
+    parts, meta = [], []
     for n in names:
         a = local[n]
         t = a if torch.is_tensor(a) else torch.from_numpy(np.ascontiguousarray(a))
@@ -68,16 +70,26 @@ def gather_results(local: Dict[str, object], total: int, world: int, rank: int, 
             t = t.to(device)
         if t.shape[0] != sizes[rank]:
             raise ValueError(f"{n}: leading dimension {t.shape[0]} != shard size {sizes[rank]}")
-        if t.shape[0] != cap:
-            pad = torch.zeros((cap,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
-            pad[: t.shape[0]] = t
-            t = pad
-        t = t.contiguous()
-        bufs = [torch.empty_like(t) for _ in range(world)]
-        dist.all_gather(bufs, t)
-        if rank == 0:
-            full = torch.cat([bufs[r][: int(sizes[r])] for r in range(world)], dim=0)
-            out[n] = full.cpu().numpy() if to_numpy else full
+        rows = t.shape[0]
+        b = t.contiguous().reshape(rows, -1).view(torch.uint8)   # [rows, bytes per instance of this array]
+        parts.append(b)
+        meta.append((n, t.dtype, tuple(t.shape[1:]), b.shape[1]))
+    packed = torch.cat(parts, dim=1) if len(parts) > 1 else parts[0]
+    if packed.shape[0] != cap:
+        pad = torch.zeros((cap, packed.shape[1]), dtype=torch.uint8, device=packed.device)
+        pad[: packed.shape[0]] = packed
+        packed = pad
+    packed = packed.contiguous()
+    full = torch.empty((world * cap, packed.shape[1]), dtype=torch.uint8, device=packed.device)
+    dist.all_gather_into_tensor(full, packed)
+    if rank != 0:
+        return None
+    keep = torch.cat([full[r * cap: r * cap + int(sizes[r])] for r in range(world)], dim=0) if int(sizes.min()) != cap else full
+    out, col = {}, 0
+    for n, dtype, tail, nb in meta:
+        v = keep[:, col: col + nb].contiguous().view(dtype).reshape((keep.shape[0],) + tail)
+        col += nb
+        out[n] = v.cpu().numpy() if to_numpy else v
     return out
 
 
