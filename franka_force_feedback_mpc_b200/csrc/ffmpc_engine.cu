@@ -54,6 +54,7 @@ struct Sub {
   // while they cross PCIe (the export staging range is reused only after `copied`)
   cudaStream_t copy = nullptr;
   cudaEvent_t exported = nullptr, copied = nullptr;
+  cudaEvent_t phase = nullptr;   // asynchronous host pipeline: recorded when this sub-batch is 1/S of a solve ahead (host_enqueue)
   bool copy_pending = false;
 };
 
@@ -265,7 +266,8 @@ int check_in(const ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters) {
 }
 
 // the launch sequence of one sub-batch solve on stream `st` (ws already bound)
-int launch_solve(ffmpc_handle *h, const Workspace &wsb, cudaStream_t st, int max_iters, int &launches) {
+int launch_solve(ffmpc_handle *h, const Workspace &wsb, cudaStream_t st, int max_iters, int &launches, cudaEvent_t signal = nullptr,
+                 int signal_after_iter = 0) {
   Params P;
   P.mdl = h->mdl;
   P.cfg = h->cfg;
@@ -292,6 +294,7 @@ int launch_solve(ffmpc_handle *h, const Workspace &wsb, cudaStream_t st, int max
     const int nfwd = launch_forward_coop(P, it, st);
     if (int e = mark(h, st, FFMPC_FAM_FORWARD, nfwd)) return e;
     launches += 3 + nfwd;
+    if (signal && it == signal_after_iter) CU(cudaEventRecord(signal, st));
   }
   CU(cudaGetLastError());
   return FFMPC_OK;
@@ -503,7 +506,8 @@ int ffmpc_create_ex(const ffmpc_config *cfg, const ffmpc_model *model, int devic
         cudaStreamCreateWithFlags(&sb.copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&sb.done, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&sb.exported, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&sb.copied, cudaEventDisableTiming) != cudaSuccess)
+        cudaEventCreateWithFlags(&sb.copied, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sb.phase, cudaEventDisableTiming) != cudaSuccess)
       rc = fail(FFMPC_ERR_CUDA, "sub-batch stream / event creation failed");
     if (rc == FFMPC_OK) rc = alloc_workspace(h, sb.ws, (size_t)h->cap);
   }
@@ -529,6 +533,7 @@ void ffmpc_destroy(ffmpc_handle *h) {
     if (sb.done) cudaEventDestroy(sb.done);
     if (sb.exported) cudaEventDestroy(sb.exported);
     if (sb.copied) cudaEventDestroy(sb.copied);
+    if (sb.phase) cudaEventDestroy(sb.phase);
     if (sb.copy) cudaStreamDestroy(sb.copy);
     if (sb.stream) cudaStreamDestroy(sb.stream);
     if (sb.stream_desc) cudaStreamDestroy(sb.stream_desc);
@@ -620,6 +625,12 @@ int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int f
   // buffers to get asynchronous copies.
   const int set = timed ? 1 : 0;
   if (int e = use_set(h, set)) return e;
+  // Asynchronous pipeline, first call after a wait: sub-batch c starts when sub-batch c-1 is 1/S of a solve ahead.  The
+  // streams (one priority) keep that offset over the following calls, so the sub-batches finish a 1/S step apart: their
+  // result copies spread over the step instead of all landing at its end (and the last call's exposed copy is one
+  // sub-batch's, not the whole batch's), and the streams sit in different kernel families at any time.
+  const bool offset = fan && !timed && h->pending_B == 0 && max_iters >= (int)chunks.size();
+  const int lead = std::max(1, max_iters / (int)chunks.size()) - 1;
   if (timed) CU(cudaEventRecord(h->ev0, h->stream));
   int launches = 0;
   for (size_t c = 0; c < chunks.size(); ++c) {
@@ -627,6 +638,7 @@ int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int f
     cudaStream_t st = sub_stream(h, c, chunks.size(), h->stream, set);
     const size_t off = chunks[c].off, cnt = chunks[c].cnt;
     if (fan && timed) CU(cudaStreamWaitEvent(st, h->ev0, 0));
+    if (offset && c > 0) CU(cudaStreamWaitEvent(st, h->subs[c - 1].phase, 0));
 #define H2D(dst, src, per, T) CU(cudaMemcpyAsync((dst) + off * (per), (src) + off * (per), cnt * (per) * sizeof(T), cudaMemcpyHostToDevice, st))
     H2D(h->d_mode, in->mode, 1, int);
     H2D(h->d_x0, in->x0, nx, double);
@@ -639,7 +651,7 @@ int host_enqueue(ffmpc_handle *h, const ffmpc_batch_in *in, int max_iters, int f
 #undef H2D
     if (c == 0) { if (int e = mark(h, st, -1, 0)) return e; }
     bind_chunk(sb.ws, &din, chunks[c], max_iters, fixed_iters);
-    rc = launch_solve(h, sb.ws, st, max_iters, launches);
+    rc = launch_solve(h, sb.ws, st, max_iters, launches, offset ? sb.phase : nullptr, lead);
     // the previous call's results of this staging range must have left before the export overwrites them
     if (rc == FFMPC_OK && sb.copy_pending) CU(cudaStreamWaitEvent(st, sb.copied, 0));
     if (rc == FFMPC_OK) rc = launch_export(h, sb.ws, st, &dout, off, launches);
