@@ -218,3 +218,27 @@ def test_golden_consumer_on_an_oracle_made_file(emu, orc):
         warnings.simplefilter("always")
         differing = check_against_golden(g, lambda cfg, am, B: _engine(emu, cfg, am, B), tol=1e-7)
     assert differing == ["mass"] and any("mass" in str(x.message) for x in w)
+
+
+def test_emulated_async_host_pipeline_equals_blocking_calls(emu):
+    """ffmpc_solve_batch_host_async + ffmpc_wait with several sub-batches (copy streams, export staging reuse, the 1/S start
+    offset of a new pipeline): same bits as the blocking call.  (The emulator runs streams in order; this covers the host
+    logic of the entry point, the GPU test covers the concurrency.)"""
+    from franka_force_feedback_mpc_b200.batch import alloc_outputs, outputs_abi
+
+    B, N, iters = 6, 8, 3
+    cfg, am, inp = make_case(True, 1, B, N, 31, 0.5)
+    eng = _engine(emu, cfg, am, B, sub_batches=3)
+    want = ("xs", "us", "K", "k", "cost", "iters", "ok", "f_pred")
+    ref = eng.solve_host(inp, iters, True, want=want)
+    outs = [alloc_outputs(B, N, 21, want) for _ in range(2)]
+    s_in = inp.to_abi()
+    for o in outs:
+        eng.solve_host_ptrs_async(s_in, outputs_abi(o), iters, True)
+    eng.wait()
+    eng.solve_host_ptrs_async(s_in, outputs_abi(outs[0]), iters, True)   # a new pipeline after the wait
+    eng.wait()
+    eng.close()
+    for o in outs:
+        for k in want:
+            assert np.array_equal(o[k], ref[k], equal_nan=True), k
