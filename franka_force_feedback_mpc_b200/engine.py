@@ -117,7 +117,7 @@ def node_eval_static(cfg, model, inp: BatchInputs, inst, knot, x, u, device: int
 
 
 class FFMPCEngine:
-    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec" | "grouped" | "tail"
+    """One handle per GPU (``ffmpc_create_ex``).  ``line_search``: "auto" | "queue" | "spec" | "grouped" | "tail" | "fill"
     (the schedule of step-length groups, ``FFMPC_LS_*``); ``sub_batches``: into how many
     concurrently scheduled sub-batches (own workspace + stream) a batch is split (0 = auto).  Both only schedule work:
     results are bit-identical."""

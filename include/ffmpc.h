@@ -193,8 +193,8 @@ void ffmpc_default_config(ffmpc_config *cfg, int variant);
 typedef struct ffmpc_options {
   int line_search; /* FFMPC_LS_*                                                                                     */
   int sub_batches; /* A batch is solved as up to this many contiguous sub-batches, each with its own workspace and
-                      CUDA stream, stream priority falling with the index: later sub-batches fill what the earlier
-                      ones leave idle (kernel tails, the late line-search passes), and in the host API a finished
+                      CUDA streams: sub-batches fill what the others leave idle (kernel tails, the late line-search
+                      passes), kernels of different families run side by side, and in the host API a finished
                       sub-batch's results cross PCIe while the others are still solved.  0 = auto (1 below 4096
                       instances of capacity, 2 below 32768, else 4), 1 = none, up to FFMPC_MAX_SUB_BATCHES.         */
   int reserved[6];
