@@ -81,6 +81,9 @@ def parse_args():
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
     ap.add_argument("--sub-batches", type=int, default=0, help="ffmpc_options.sub_batches (0 = auto)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default, the driver's contract): --batch instances on EVERY GPU, and a `strong` block beside it; "
+                         "strong: --batch instances IN TOTAL sharded over the GPUs (BASELINE configs[3] as written) as the line's value")
     ap.add_argument("--tick-stream-ticks", type=int, default=600, help="ticks of the B = 1 latency streams (configs 1, 2)")
     ap.add_argument("--no-also", action="store_true", help="skip the short BASELINE config 3 / config 5 runs")
     a = ap.parse_args()
@@ -344,7 +347,19 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     B, N = args.batch, args.horizon
-    cfg, model, inp, nx = make_problem(args, rank, B)
+    total = world * B
+    if args.scaling == "strong" and world > 1:
+        # the one global sweep (rank-0 seeds), this rank's contiguous slice of it
+        from franka_force_feedback_mpc_b200 import sharding as _sh
+
+        lo, hi = _sh.shard_bounds(args.batch, world, rank)
+        cfg, model, ginp, nx = make_problem(args, 0, args.batch)
+        inp = ginp.slice(np.arange(lo, hi))
+        total, B = args.batch, int(_sh.shard_sizes(args.batch, world).max())
+        if inp.B != B:   # ragged split: pad this rank's shard with copies of its last instance (timing only; work is max over ranks)
+            inp = inp.slice(np.minimum(np.arange(B), inp.B - 1))
+    else:
+        cfg, model, inp, nx = make_problem(args, rank, B)
     nc = (3 if args.contact_model == "point3d" else 1) if args.contact_fraction > 0 else 0
     eng = engine.FFMPCEngine(cfg, model, device=local_rank, max_batch=B, sub_batches=args.sub_batches)
 
@@ -452,7 +467,7 @@ def main():
     # the per-instance results cost / iters / ok / f_pred are gathered from device memory over NCCL inside the timed region
     # (north_star: "only a final result gather over NVLink"); no collective on the solve path.
     strong = None
-    if world > 1:
+    if world > 1 and args.scaling == "weak":
         from franka_force_feedback_mpc_b200 import sharding
 
         lo, hi = sharding.shard_bounds(B, world, rank)
@@ -543,8 +558,8 @@ def main():
             rollouts = cpu.get("rollouts_per_iteration") or 1.0
         else:  # the CPU baseline is an N = 1 figure; here a 1 s sample only counts the rollouts of the line search (FLOP model)
             rollouts = cpu_baseline(args, cfg, model, inp, nthreads, seconds=1.0).get("rollouts_per_iteration") or 1.0
-    value = world * B * args.steps / (ms_total * 1e-3)
-    e2e_val = world * B * args.steps / e2e_s
+    value = total * args.steps / (ms_total * 1e-3)
+    e2e_val = total * args.steps / e2e_s
     peak_tf = engine.dfma_peak_tflops(local_rank)
     knots = B * (N + 1)
     fam_flop = {
@@ -606,12 +621,12 @@ def main():
                 "config5": short_run(args, local_rank, "ff", "point3d", 16384, 20, 0.75)}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_config(args, B, nx),
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ok": e2e_ok,
                 "call": "ffmpc_solve_batch_host_async x steps + ffmpc_wait (pinned host buffers; every step copies its inputs in and its "
                         "results out)",
-                "blocking_call_value": world * B * args.steps / e2e_sync_s, "d2h_gbs_rank0": d2h_gbs_rank,
+                "blocking_call_value": total * args.steps / e2e_sync_s, "d2h_gbs_rank0": d2h_gbs_rank,
                 "numa_rank0": numa},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "latency": latency, "all_iters_ran": ok_dev,
